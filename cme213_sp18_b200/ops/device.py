@@ -1,0 +1,322 @@
+"""torch-facing wrappers over the hand-written sm_100a kernels in libcme213b.so.
+
+Every function here launches this repo's own CUDA kernels through the C ABI declared in
+include/cme213b.h; none of them falls back to a PyTorch op.  A module-level launch counter
+(`launches()`) counts kernel launches issued through this module so benches can report how
+many of the repo's kernels ran inside a timed region.
+"""
+from __future__ import annotations
+
+import torch
+
+from ._lib import check, device_lib, ptr, require_cuda, stream_ptr
+
+_launches = 0
+
+
+def launches() -> int:
+    return _launches
+
+
+def _count(n: int = 1) -> None:
+    global _launches
+    _launches += n
+
+
+def device_info():
+    import ctypes as C
+
+    sm, maj, mnr = C.c_int(0), C.c_int(0), C.c_int(0)
+    check(device_lib().cme_device_info(C.addressof(sm), C.addressof(maj), C.addressof(mnr)),
+          "cme_device_info")
+    return {"sm_count": sm.value, "cc": (maj.value, mnr.value)}
+
+
+# ------------------------------------------------------------------ hw2 q1
+SHIFT_VARIANTS = {"char": 0, "uint": 1, "uint2": 2, "uint4": 3}
+
+
+def shift_bytes(src: torch.Tensor, shift: int, variant: str = "uint4",
+                out: torch.Tensor | None = None) -> torch.Tensor:
+    """out[i] = src[i] + shift mod 256 (ref hw2code/shift.cu:13-99)."""
+    require_cuda(src)
+    assert src.dtype == torch.uint8 and src.is_contiguous()
+    if out is None:
+        out = torch.empty_like(src)
+    check(device_lib().cme_shift_bytes(ptr(src), ptr(out), src.numel(), shift & 0xFF,
+                                       SHIFT_VARIANTS[variant], stream_ptr()), "cme_shift_bytes")
+    _count(1 if src.numel() % 16 == 0 or variant == "char" else 2)
+    return out
+
+
+# ------------------------------------------------------------------ hw2 q2
+def pagerank_prescale(rank: torch.Tensor, inv_deg: torch.Tensor, contrib: torch.Tensor) -> None:
+    check(device_lib().cme_pagerank_prescale(ptr(rank), ptr(inv_deg), ptr(contrib), rank.numel(),
+                                             stream_ptr()), "cme_pagerank_prescale")
+    _count()
+
+
+def pagerank_step(row_ptr, edges_ptr: int, contrib_in, inv_deg, rank_out, contrib_out,
+                  row_begin: int, row_end: int, num_nodes: int, peer_contrib: torch.Tensor | None = None,
+                  nranks: int = 1) -> None:
+    """One propagation step (ref hw2code/pagerank.cu:9-28). edges_ptr is an address so a
+    row-partitioned caller can pass (local_edges - first_local_edge)."""
+    check(device_lib().cme_pagerank_step(ptr(row_ptr), edges_ptr, ptr(contrib_in), ptr(inv_deg),
+                                         ptr(rank_out), ptr(contrib_out), ptr(peer_contrib), nranks,
+                                         row_begin, row_end, num_nodes, stream_ptr()),
+          "cme_pagerank_step")
+    _count()
+
+
+def pagerank_gen_edges(edges: torch.Tensor, edge_begin: int, num_nodes: int, seed: int) -> None:
+    check(device_lib().cme_pagerank_gen_edges(ptr(edges), edge_begin, edges.numel(), num_nodes,
+                                              seed, stream_ptr()), "cme_pagerank_gen_edges")
+    _count()
+
+
+# ------------------------------------------------------------------ hw3
+HEAT_VARIANTS = {"global": 0, "loop": 1, "shared": 2}
+
+
+def heat_step(nxt: torch.Tensor, cur: torch.Tensor, order: int, xcfl: float, ycfl: float,
+              variant: str = "shared", bc_scale: float | None = None) -> None:
+    """One time step of the 2-D heat stencil (ref hw3code/gpuStencil.cu:62-74, 163-179).
+    If bc_scale is given the border decay rides in the same launch (ref hw3code/BC.h:7-38)."""
+    require_cuda(nxt, cur)
+    gy, gx = cur.shape
+    check(device_lib().cme_heat_step(ptr(nxt), ptr(cur), gx, gy, order, xcfl, ycfl,
+                                     HEAT_VARIANTS[variant], 0 if bc_scale is None else 1,
+                                     0.0 if bc_scale is None else bc_scale, stream_ptr()),
+          "cme_heat_step")
+    _count()
+
+
+def heat_bc(nxt: torch.Tensor, cur: torch.Tensor, order: int, bc_scale: float) -> None:
+    gy, gx = cur.shape
+    check(device_lib().cme_heat_bc(ptr(nxt), ptr(cur), gx, gy, order, bc_scale, stream_ptr()),
+          "cme_heat_bc")
+    _count()
+
+
+def heat_slab_step(nxt: torch.Tensor, cur: torch.Tensor, up_ghost_ptr: int | None,
+                   down_ghost_ptr: int | None, rows_local: int, order: int, xcfl: float,
+                   ycfl: float, bc_scale: float, is_top: bool, is_bottom: bool) -> None:
+    gx = cur.shape[1]
+    check(device_lib().cme_heat_slab_step(ptr(nxt), ptr(cur), up_ghost_ptr, down_ghost_ptr, gx,
+                                          rows_local, order, xcfl, ycfl, bc_scale, int(is_top),
+                                          int(is_bottom), stream_ptr()), "cme_heat_slab_step")
+    _count()
+
+
+# ------------------------------------------------------------------ hw4
+def sanitize_compact(raw: torch.Tensor):
+    """Lower-case and keep letters only (ref hw4code/create_cipher.cu:184-195).
+    Returns (buffer, count tensor); buffer[:count] is the clean text."""
+    require_cuda(raw)
+    n = raw.numel()
+    out = torch.empty(max(n, 1), dtype=torch.uint8, device=raw.device)
+    count = torch.zeros(1, dtype=torch.int64, device=raw.device)
+    scratch = torch.empty(4 * (n // 2048 + 2) + 16, dtype=torch.uint8, device=raw.device)
+    check(device_lib().cme_sanitize_compact(ptr(raw), n, ptr(out), ptr(count), ptr(scratch),
+                                            scratch.numel(), stream_ptr()), "cme_sanitize_compact")
+    _count(3)
+    return out, count
+
+
+def byte_histogram(text: torch.Tensor, stride: int = 1, offset: int = 0) -> torch.Tensor:
+    require_cuda(text)
+    counts = torch.empty(256, dtype=torch.int64, device=text.device)
+    check(device_lib().cme_byte_histogram(ptr(text), text.numel(), stride, offset, ptr(counts),
+                                          stream_ptr()), "cme_byte_histogram")
+    _count()
+    return counts
+
+
+def strided_histograms(text: torch.Tensor, period: int) -> torch.Tensor:
+    require_cuda(text)
+    counts = torch.empty((period, 256), dtype=torch.int64, device=text.device)
+    check(device_lib().cme_strided_histograms(ptr(text), text.numel(), period, ptr(counts),
+                                              stream_ptr()), "cme_strided_histograms")
+    _count()
+    return counts
+
+
+def vigenere_shift(text: torch.Tensor, shifts: torch.Tensor, wrap26: bool = False) -> torch.Tensor:
+    require_cuda(text, shifts)
+    assert shifts.dtype == torch.int32
+    out = torch.empty_like(text)
+    check(device_lib().cme_vigenere_shift(ptr(text), ptr(out), text.numel(), ptr(shifts),
+                                          shifts.numel(), int(wrap26), stream_ptr()),
+          "cme_vigenere_shift")
+    _count()
+    return out
+
+
+def lag_match_counts(text: torch.Tensor, lag0: int, num_lags: int) -> torch.Tensor:
+    require_cuda(text)
+    out = torch.empty(num_lags, dtype=torch.int64, device=text.device)
+    check(device_lib().cme_lag_match_counts(ptr(text), text.numel(), lag0, num_lags, ptr(out),
+                                            stream_ptr()), "cme_lag_match_counts")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------ hw1 on the GPU
+def parity_sum(values: torch.Tensor) -> torch.Tensor:
+    require_cuda(values)
+    assert values.dtype in (torch.uint32, torch.int32)
+    out = torch.empty(2, dtype=torch.int64, device=values.device)
+    check(device_lib().cme_parity_sum(ptr(values), values.numel(), ptr(out), stream_ptr()),
+          "cme_parity_sum")
+    _count()
+    return out
+
+
+def radix_sort(keys: torch.Tensor) -> torch.Tensor:
+    """Stable LSD radix sort of 32-bit keys, treated as unsigned. Returns a sorted copy."""
+    require_cuda(keys)
+    assert keys.dtype in (torch.uint32, torch.int32) and keys.is_contiguous()
+    k = keys.clone()
+    tmp = torch.empty_like(k)
+    nbytes = int(device_lib().cme_radix_scratch_bytes(k.numel()))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=k.device)
+    check(device_lib().cme_radix_sort(ptr(k), ptr(tmp), k.numel(), ptr(scratch), nbytes,
+                                      stream_ptr()), "cme_radix_sort")
+    _count(12)
+    return k
+
+
+# ------------------------------------------------------------------ fp64 parity path
+def dgemm(transA: bool, transB: bool, M: int, N: int, K: int, alpha: float, A: torch.Tensor, lda: int,
+          B: torch.Tensor, ldb: int, beta: float, Cm: torch.Tensor, ldc: int) -> None:
+    """Column-major C = alpha*op(A)*op(B) + beta*C (ref fpcode/gpu_func.cu:259-297)."""
+    require_cuda(A, B, Cm)
+    assert A.dtype == B.dtype == Cm.dtype == torch.float64
+    check(device_lib().cme_dgemm(int(transA), int(transB), M, N, K, alpha, ptr(A), lda, ptr(B), ldb,
+                                 beta, ptr(Cm), ldc, stream_ptr()), "cme_dgemm")
+    _count()
+
+
+def d_bias_sigmoid(z, bias, rows, cols):
+    check(device_lib().cme_d_bias_sigmoid(ptr(z), ptr(bias), rows, cols, stream_ptr()),
+          "cme_d_bias_sigmoid")
+    _count()
+
+
+def d_bias_softmax_ce(z, bias, labels, diff, scale, loss_sum, rows, cols):
+    check(device_lib().cme_d_bias_softmax_ce(ptr(z), ptr(bias), ptr(labels), ptr(diff), scale,
+                                             ptr(loss_sum), rows, cols, stream_ptr()),
+          "cme_d_bias_softmax_ce")
+    _count()
+
+
+def d_dsigmoid(da, a, dz):
+    check(device_lib().cme_d_dsigmoid(ptr(da), ptr(a), ptr(dz), a.numel(), stream_ptr()),
+          "cme_d_dsigmoid")
+    _count()
+
+
+def d_row_sum(m, out, rows, cols):
+    check(device_lib().cme_d_row_sum(ptr(m), ptr(out), rows, cols, stream_ptr()), "cme_d_row_sum")
+    _count()
+
+
+def d_sgd(p, g, lr, reg):
+    check(device_lib().cme_d_sgd(ptr(p), ptr(g), p.numel(), lr, reg, stream_ptr()), "cme_d_sgd")
+    _count()
+
+
+def d_axpby(c, a, b, alpha, beta):
+    check(device_lib().cme_d_axpby(ptr(c), ptr(a), ptr(b), alpha, beta, c.numel(), stream_ptr()),
+          "cme_d_axpby")
+    _count()
+
+
+# ------------------------------------------------------------------ bf16 tensor-core path
+def u8_to_bf16_rows(src_ptr: int, dst: torch.Tensor, rows: int, cols: int, add_ones: bool = True) -> None:
+    """uint8 rows -> bf16 rows of dst (leading dim = dst.shape[1]); src_ptr may be a peer address
+    (the minibatch scatter, ref fpcode/neural_network.cpp:460-481)."""
+    ld = dst.shape[1]
+    check(device_lib().cme_u8_to_bf16_rows(src_ptr, ptr(dst), rows, cols, ld, int(add_ones),
+                                           stream_ptr()), "cme_u8_to_bf16_rows")
+    _count()
+
+
+def mlp_fwd1(X: torch.Tensor, W1c: torch.Tensor, A1: torch.Tensor, rows: int, K: int, H: int) -> None:
+    """A1 = sigmoid(X @ W1c.T) on tcgen05 (ref fpcode/neural_network.cpp:289-300)."""
+    check(device_lib().cme_mlp_fwd1(ptr(X), ptr(W1c), None, ptr(A1), rows, K, H, X.shape[1],
+                                    A1.shape[1], stream_ptr()), "cme_mlp_fwd1")
+    _count()
+
+
+def gemm_bf16(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """C[M,N] = A[M,K] @ B[N,K].T in bf16 with fp32 accumulation on tcgen05."""
+    require_cuda(A, B)
+    assert A.dtype == B.dtype == torch.bfloat16 and A.stride(1) == 1 and B.stride(1) == 1
+    M, K = A.shape
+    N = B.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=A.device)
+    check(device_lib().cme_gemm_bf16(ptr(A), ptr(B), ptr(out), M, N, K, A.stride(0), B.stride(0),
+                                     out.stride(0), stream_ptr()), "cme_gemm_bf16")
+    _count()
+    return out
+
+
+def mlp_fwd2_softmax(A1, W2, b2, labels, dz2, loss_sum, pred, gb2, scale: float, rows: int, H: int,
+                     C: int = 10) -> None:
+    check(device_lib().cme_mlp_fwd2_softmax(ptr(A1), ptr(W2), ptr(b2), ptr(labels), ptr(dz2),
+                                            ptr(loss_sum), ptr(pred), ptr(gb2), scale, rows, H,
+                                            A1.shape[1], C, stream_ptr()), "cme_mlp_fwd2_softmax")
+    _count()
+
+
+def mlp_bwd_elem(A1, dz2, W2, dZ1, gW2, rows: int, H: int, C: int = 10) -> None:
+    check(device_lib().cme_mlp_bwd_elem(ptr(A1), ptr(dz2), ptr(W2), ptr(dZ1), ptr(gW2), rows, H,
+                                        A1.shape[1], C, stream_ptr()), "cme_mlp_bwd_elem")
+    _count()
+
+
+def mlp_dw1(dZ1, X, gW1, rows: int, K: int, H: int, ldg: int) -> None:
+    check(device_lib().cme_mlp_dw1(ptr(dZ1), ptr(X), ptr(gW1), rows, K, H, X.shape[1], dZ1.shape[1],
+                                   ldg, stream_ptr()), "cme_mlp_dw1")
+    _count()
+
+
+def _ptr_table(ptrs):
+    import ctypes as C
+
+    arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
+    return arr
+
+
+def allreduce_sgd(grad_ptrs, param_ptrs, w1c_ptrs, rank: int, n_total: int, n_w1: int, ldx: int,
+                  kreg: int, w2_begin: int, w2_end: int, lr: float, reg: float) -> None:
+    """Fused gradient all-reduce + L2 + SGD + bf16 re-cast over peer pointers
+    (ref fpcode/neural_network.cpp:501-541)."""
+    n = len(grad_ptrs)
+    check(device_lib().cme_allreduce_sgd(_ptr_table(grad_ptrs), _ptr_table(param_ptrs),
+                                         _ptr_table(w1c_ptrs), rank, n, n_total, n_w1, ldx, kreg,
+                                         w2_begin, w2_end, lr, reg, stream_ptr()), "cme_allreduce_sgd")
+    _count()
+
+
+def allreduce_sgd_mc(mc_grads: int, local_params: int, mc_params: int, mc_w1c: int, rank: int,
+                     nranks: int, n_total: int, n_w1: int, ldx: int, kreg: int, w2_begin: int,
+                     w2_end: int, lr: float, reg: float) -> None:
+    check(device_lib().cme_allreduce_sgd_mc(mc_grads, local_params, mc_params, mc_w1c, rank, nranks,
+                                            n_total, n_w1, ldx, kreg, w2_begin, w2_end, lr, reg,
+                                            stream_ptr()), "cme_allreduce_sgd_mc")
+    _count()
+
+
+def peer_barrier(pads_dev: torch.Tensor, rank: int, nranks: int, channel: int, epoch: int,
+                 signal: bool = True, wait: bool = True) -> None:
+    check(device_lib().cme_peer_barrier(ptr(pads_dev), rank, nranks, channel, epoch & 0xFFFFFFFF,
+                                        int(signal), int(wait), stream_ptr()), "cme_peer_barrier")
+    _count()
+
+
+def peer_copy(src_ptr: int, dst: torch.Tensor, nbytes: int) -> None:
+    check(device_lib().cme_peer_copy(src_ptr, ptr(dst), nbytes, stream_ptr()), "cme_peer_copy")
+    _count()

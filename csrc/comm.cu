@@ -1,0 +1,220 @@
+// Cross-GPU pieces over NVLink 5 / NVSwitch peer memory (no MPI, no NCCL here).
+//
+// The reference moves every minibatch through host memory: D2H of four gradient
+// buffers, four MPI_Allreduce calls on host memory, SGD on the host, and a full
+// H2D re-upload of the weights next step (ref fpcode/neural_network.cpp:484-541).
+// Here the gradient all-reduce, the L2 term, the SGD step and the bf16 re-cast
+// of the weights are ONE kernel that reads its slice of every rank's gradient
+// buffer through peer-mapped pointers (or one multimem.ld_reduce through the
+// NVSwitch multicast address) and writes the updated weights into every rank's
+// replica.  Flags for ordering between ranks are plain uint32 slots in a
+// peer-mapped pad, bumped with release atomics and polled with acquire loads.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxRanks = 16;
+
+struct PeerPtrs {
+    float* grads[kMaxRanks];
+    float* params[kMaxRanks];
+    __nv_bfloat16* w1c[kMaxRanks];
+};
+
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+    float4 r;
+    // peer data changes every step: never serve it from a stale L1 line
+    asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
+// reg applies to W1 entries (column < kreg of each ldx-long row) and to the W2
+// block [w2_begin, w2_end); biases and pad entries get none
+__device__ __forceinline__ float reg_for(int64_t i, int64_t n_w1, int ldx, int kreg,
+                                         int64_t w2_begin, int64_t w2_end, float reg) {
+    if (i < n_w1) return ((int)(i % ldx) < kreg) ? reg : 0.f;
+    return (i >= w2_begin && i < w2_end) ? reg : 0.f;
+}
+
+__global__ void __launch_bounds__(256)
+allreduce_sgd_p2p_kernel(PeerPtrs pp, int rank, int nranks, int64_t begin, int64_t end,
+                         int64_t n_w1, int ldx, int kreg, int64_t w2_begin, int64_t w2_end,
+                         float lr, float reg) {
+    const int64_t gstride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i = begin + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < end;
+         i += gstride) {
+        // fixed summation order (rank 0, 1, ...) so every configuration is reproducible
+        float4 s = ld_peer_f4(pp.grads[0] + i);
+        for (int r = 1; r < nranks; ++r) {
+            const float4 g = ld_peer_f4(pp.grads[r] + i);
+            s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+        }
+        const float4 p = *reinterpret_cast<const float4*>(pp.params[rank] + i);
+        float4 q;
+        q.x = p.x - lr * (s.x + reg_for(i, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.x);
+        q.y = p.y - lr * (s.y + reg_for(i + 1, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.y);
+        q.z = p.z - lr * (s.z + reg_for(i + 2, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.z);
+        q.w = p.w - lr * (s.w + reg_for(i + 3, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.w);
+        const bool in_w1 = i < n_w1;
+        const uint2 qb = make_uint2(pack2(q.x, q.y), pack2(q.z, q.w));
+        for (int r = 0; r < nranks; ++r) {
+            *reinterpret_cast<float4*>(pp.params[r] + i) = q;
+            if (in_w1) *reinterpret_cast<uint2*>(pp.w1c[r] + i) = qb;
+        }
+    }
+}
+
+// NVSwitch multicast variant: the switch performs the sum (multimem.ld_reduce)
+// and replicates the stores (multimem.st) to every GPU bound to the address.
+__global__ void __launch_bounds__(256)
+allreduce_sgd_mc_kernel(const float* __restrict__ mc_grads, float* __restrict__ local_params,
+                        float* __restrict__ mc_params, __nv_bfloat16* __restrict__ mc_w1c,
+                        int64_t begin, int64_t end, int64_t n_w1, int ldx, int kreg,
+                        int64_t w2_begin, int64_t w2_end, float lr, float reg) {
+    const int64_t gstride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i = begin + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < end;
+         i += gstride) {
+        float4 s;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(s.x), "=f"(s.y), "=f"(s.z), "=f"(s.w)
+                     : "l"(mc_grads + i)
+                     : "memory");
+        const float4 p = *reinterpret_cast<const float4*>(local_params + i);
+        float4 q;
+        q.x = p.x - lr * (s.x + reg_for(i, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.x);
+        q.y = p.y - lr * (s.y + reg_for(i + 1, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.y);
+        q.z = p.z - lr * (s.z + reg_for(i + 2, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.z);
+        q.w = p.w - lr * (s.w + reg_for(i + 3, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.w);
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_params + i),
+                     "f"(q.x), "f"(q.y), "f"(q.z), "f"(q.w)
+                     : "memory");
+        if (i < n_w1) {
+            const float b0 = __uint_as_float(pack2(q.x, q.y)), b1 = __uint_as_float(pack2(q.z, q.w));
+            asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc_w1c + i),
+                         "f"(b0), "f"(b1)
+                         : "memory");
+        }
+    }
+}
+
+// signal every peer, then wait until every peer has signalled `epoch` times
+__global__ void peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank, int nranks,
+                                    int channel, uint32_t epoch, int do_signal, int do_wait) {
+    const int r = threadIdx.x;
+    if (r >= nranks) return;
+    if (do_signal) {
+        __threadfence_system();
+        uint32_t* slot = pads[r] + channel * 64 + rank;
+        asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(slot) : "memory");
+    }
+    if (do_wait) {
+        const uint32_t* mine = pads[rank] + channel * 64 + r;
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+        } while ((int32_t)(v - epoch) < 0);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n16) {
+    constexpr int U = 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + (U - 1) * stride < n16; i += U * stride) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) v[u] = cme::ld_stream_u4(src + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < U; ++u) dst[i + u * stride] = v[u];
+    }
+    for (; i < n16; i += stride) dst[i] = cme::ld_stream_u4(src + i);
+}
+
+int slice_bounds(int64_t n_total, int rank, int nranks, int64_t* b, int64_t* e) {
+    // slices are multiples of 4 floats so every access is a 16-byte vector
+    const int64_t quads = n_total / 4;
+    *b = quads * rank / nranks * 4;
+    *e = quads * (rank + 1) / nranks * 4;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cme_allreduce_sgd(float* const* grads_host, float* const* params_host, void* const* w1c_host,
+                      int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
+                      int64_t w2_begin, int64_t w2_end, float lr, float reg, void* stream) {
+    CME_CHECK_ARG(grads_host && params_host && w1c_host, "cme_allreduce_sgd: null pointer table");
+    CME_CHECK_ARG(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks,
+                  "cme_allreduce_sgd: rank %d of %d", rank, nranks);
+    CME_CHECK_ARG(n_total % 4 == 0 && n_w1 % 4 == 0 && ldx % 4 == 0 && n_w1 <= n_total,
+                  "cme_allreduce_sgd: sizes must be multiples of 4 floats");
+    PeerPtrs pp;
+    for (int r = 0; r < nranks; ++r) {
+        pp.grads[r] = grads_host[r];
+        pp.params[r] = params_host[r];
+        pp.w1c[r] = (__nv_bfloat16*)w1c_host[r];
+        CME_CHECK_ARG(pp.grads[r] && pp.params[r] && pp.w1c[r], "cme_allreduce_sgd: null peer %d", r);
+    }
+    int64_t b, e;
+    slice_bounds(n_total, rank, nranks, &b, &e);
+    if (e <= b) return 0;
+    const int grid = cme::stride_grid((e - b) / 4, 256, 4, 2);
+    allreduce_sgd_p2p_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
+        pp, rank, nranks, b, e, n_w1, ldx, kreg, w2_begin, w2_end, lr, reg);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_params,
+                         void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
+                         int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
+                         void* stream) {
+    CME_CHECK_ARG(mc_grads && local_params && mc_params && mc_w1c, "cme_allreduce_sgd_mc: null pointer");
+    CME_CHECK_ARG(nranks >= 1 && rank >= 0 && rank < nranks, "cme_allreduce_sgd_mc: rank %d of %d",
+                  rank, nranks);
+    CME_CHECK_ARG(n_total % 4 == 0 && n_w1 % 4 == 0 && ldx % 4 == 0 && n_w1 <= n_total,
+                  "cme_allreduce_sgd_mc: sizes must be multiples of 4 floats");
+    int64_t b, e;
+    slice_bounds(n_total, rank, nranks, &b, &e);
+    if (e <= b) return 0;
+    const int grid = cme::stride_grid((e - b) / 4, 256, 4, 2);
+    allreduce_sgd_mc_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
+        mc_grads, local_params, mc_params, (__nv_bfloat16*)mc_w1c, b, e, n_w1, ldx, kreg, w2_begin,
+        w2_end, lr, reg);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, uint32_t epoch,
+                     int do_signal, int do_wait, void* stream) {
+    CME_CHECK_ARG(pads && nranks >= 1 && nranks <= 32 && rank >= 0 && rank < nranks,
+                  "cme_peer_barrier: rank %d of %d", rank, nranks);
+    CME_CHECK_ARG(channel >= 0 && channel < 8, "cme_peer_barrier: channel %d not in 0..7", channel);
+    peer_barrier_kernel<<<1, 32, 0, cme::as_stream(stream)>>>(pads, rank, nranks, channel, epoch,
+                                                             do_signal, do_wait);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream) {
+    CME_CHECK_ARG(src && dst && bytes % 16 == 0, "cme_peer_copy: 16-byte multiples only");
+    if (bytes == 0) return 0;
+    const size_t n16 = bytes / 16;
+    peer_copy_kernel<<<cme::stride_grid((int64_t)n16, 256, 8, 2), 256, 0, cme::as_stream(stream)>>>(
+        (const uint4*)src, (uint4*)dst, n16);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

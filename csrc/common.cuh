@@ -1,0 +1,92 @@
+// Shared host/device helpers for the cme213b device library (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "cme213b.h"
+
+namespace cme {
+
+// ---- error plumbing ---------------------------------------------------------
+void set_error(const char* fmt, ...);
+
+#define CME_CHECK_ARG(cond, ...)              \
+    do {                                      \
+        if (!(cond)) {                        \
+            ::cme::set_error(__VA_ARGS__);    \
+            return -1;                        \
+        }                                     \
+    } while (0)
+
+#define CME_CUDA(call)                                                                  \
+    do {                                                                                \
+        cudaError_t e__ = (call);                                                       \
+        if (e__ != cudaSuccess) {                                                       \
+            ::cme::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,               \
+                             cudaGetErrorString(e__));                                  \
+            return (int)e__;                                                            \
+        }                                                                               \
+    } while (0)
+
+#define CME_LAUNCH_CHECK()                                                              \
+    do {                                                                                \
+        cudaError_t e__ = cudaGetLastError();                                           \
+        if (e__ != cudaSuccess) {                                                       \
+            ::cme::set_error("%s:%d launch -> %s", __FILE__, __LINE__,                  \
+                             cudaGetErrorString(e__));                                  \
+            return (int)e__;                                                            \
+        }                                                                               \
+    } while (0)
+
+// Cached per-process device facts (queried once for the current device).
+int sm_count();
+
+static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Grid for a grid-stride kernel: enough blocks to cover `work_items` but never
+// more than `waves` full waves of the machine (148 SMs x blocks_per_sm).
+static inline int stride_grid(int64_t work_items, int block, int blocks_per_sm, int waves = 4) {
+    int64_t need = ceil_div64(work_items, block);
+    int64_t cap = (int64_t)sm_count() * blocks_per_sm * waves;
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+}
+
+// ---- device helpers ---------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Streaming 128-bit accesses that do not allocate in L1.
+__device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream_u4(uint4* p, const uint4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+}  // namespace cme

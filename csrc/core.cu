@@ -1,0 +1,48 @@
+// Library plumbing: error string, device facts.
+#include "common.cuh"
+
+#include <mutex>
+
+namespace cme {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    // per device: a process may drive several GPUs in tests
+    static int cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+}  // namespace cme
+
+extern "C" {
+
+const char* cme_last_error(void) { return cme::g_err; }
+
+int cme_version(void) { return 100; }
+
+int cme_device_info(int* sms, int* cc_major, int* cc_minor) {
+    int dev = 0;
+    CME_CUDA(cudaGetDevice(&dev));
+    if (sms) CME_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
+    if (cc_major) CME_CUDA(cudaDeviceGetAttribute(cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (cc_minor) CME_CUDA(cudaDeviceGetAttribute(cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,503 @@
+// tcgen05 / TMEM / TMA GEMM kernels for the bf16 MLP path (sm_100a).
+//
+// Two persistent, warp-specialised kernels replace the reference's three 32x32
+// shared-memory fp64 GEMM kernels (ref fpcode/gpu_func.cu:92-256):
+//
+//   gemm_kmajor   C[M,N] = epi(A[M,K] * B[N,K]^T), both operands K-major.
+//                 Forward layer 1: A = X (minibatch rows), B = W1c, epilogue =
+//                 sigmoid, bf16 result written with TMA stores.  The bias rides
+//                 in the GEMM: X carries a column of ones and W1c carries b1 in
+//                 the matching column, so there is no bias pass (ref K8) and no
+//                 separate sigmoid pass (ref K6).
+//   gemm_mnmajor  G[M,N] += A[Kd,M]^T * B[Kd,N], both operands MN-major, the
+//                 reduction dimension is the (huge) batch.  dW1 = dZ1^T * X.
+//                 Work is split stream-K style: the (tile, k-block) space is cut
+//                 into equal contiguous ranges, one per SM, and partial tiles are
+//                 added with vector fp32 reductions, so 148 SMs stay busy for any
+//                 batch size.  The ones column of X makes column K of the result
+//                 the bias gradient (ref K7 row sums) for free.
+//
+// Roles per CTA (192 threads): warp 0 = TMA producer (one lane), warp 1 = MMA
+// issuer (one lane; also owns the TMEM allocation), warps 2-5 = epilogue (each
+// reads its 32-lane TMEM sub-partition).  Pipelines: smem full/empty ring
+// (TMA <-> MMA) and a 2-deep TMEM accumulator ring (MMA <-> epilogue).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace {
+
+using namespace tc;
+
+constexpr int kThreads = 192;
+constexpr int kStages = 4;
+constexpr int BM = 128;
+constexpr int BK = 64;                       // bf16 elements = one 128-byte swizzle row
+constexpr int kABytes = BM * BK * 2;         // 16 KB
+constexpr int kBBytesMax = 256 * BK * 2;     // 32 KB
+constexpr int kStageBytes = 64 * 128 * 2;    // 128 rows x 64 cols bf16 epilogue staging
+constexpr int kSmemKMajor = kStages * (kABytes + kBBytesMax) + 2 * kStageBytes + 1024 + 256;
+constexpr int kSmemMNMajor = kStages * (kABytes + kBBytesMax) + 1024 + 256;
+
+struct Barriers {
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t tmem_full[2];
+    uint64_t tmem_empty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
+    return (uint8_t*)(((uintptr_t)p + 1023) & ~(uintptr_t)1023);
+}
+
+__device__ __forceinline__ void setup(Barriers* bars, uint32_t tmem_cols, int warp, int lane) {
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&bars->tmem_full[a], 1);
+            mbar_init(&bars->tmem_empty[a], 4);   // one arrive per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {   // whole warp: .sync.aligned
+        tmem_alloc(&bars->tmem_base, tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+}
+
+__device__ __forceinline__ void teardown(Barriers* bars, uint32_t tmem_cols, int warp) {
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(bars->tmem_base, tmem_cols);
+    }
+}
+
+// =============================================================================
+// K-major GEMM with fused epilogue and TMA store
+// =============================================================================
+template <int EPI /* 0 = identity, 1 = sigmoid */>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                   const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K, int BN,
+                   uint32_t tmem_cols) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + kStages * kABytes;
+    uint8_t* sC = sB + kStages * kBBytesMax;
+    Barriers* bars = (Barriers*)(sC + 2 * kStageBytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        prefetch_tmap(&tmC);
+    }
+    setup(bars, tmem_cols, warp, lane);
+    const uint32_t tmem_base = bars->tmem_base;
+
+    const int num_tiles = m_tiles * n_tiles;
+    const int nk = (K + BK - 1) / BK;
+    const uint32_t b_bytes = (uint32_t)BN * BK * 2;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---------------- TMA producer ----------------
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
+                    tma_load_2d(sA + stage * kABytes, &tmA, &bars->full[stage], kb * BK, m0);
+                    tma_load_2d(sB + stage * kBBytesMax, &tmB, &bars->full[stage], kb * BK, n0);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();   // reconverge before the CTA-wide barrier in teardown()
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---------------- MMA issuer ----------------
+            const uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const int kvalid = min(BK, K - kb * BK);
+                    const int nmma = (kvalid + 15) >> 4;
+                    const uint64_t da = smem_desc_sw128(smem_u32(sA + stage * kABytes), 16, 1024);
+                    const uint64_t db = smem_desc_sw128(smem_u32(sB + stage * kBBytesMax), 16, 1024);
+                    for (int j = 0; j < nmma; ++j) {
+                        // +32 bytes per 16-element K step inside the 128-byte swizzle row
+                        umma_bf16(d_tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc,
+                                  (kb | j) != 0);
+                    }
+                    umma_commit(&bars->empty[stage]);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&bars->tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue: TMEM -> regs -> smem -> TMA store ----------------
+        const int q = warp & 3;                    // TMEM sub-partition of this warp
+        const int row = q * 32 + lane;             // row inside the 128-row tile
+        const bool leader = (warp == 2 && lane == 0);
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        int cbuf = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            for (int c = 0; c < BN / 64; ++c) {
+                // the staging buffer we are about to fill was handed to a TMA store
+                // two chunks ago: wait until that store has finished reading it
+                if (leader) tma_store_wait_read<1>();
+                named_bar_sync(1, 128);
+                uint8_t* stg = sC + cbuf * kStageBytes;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + (uint32_t)(c * 64 + half * 32), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {   // 4 x 16-byte chunks (8 bf16 each)
+                        uint32_t p[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float x0 = __uint_as_float(v[g * 8 + 2 * e]);
+                            float x1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                            if (EPI == 1) { x0 = sigmoid_fast(x0); x1 = sigmoid_fast(x1); }
+                            p[e] = pack_bf16(x0, x1);
+                        }
+                        const int chunk = half * 4 + g;                 // 16-byte chunk in the row
+                        const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+                        *reinterpret_cast<uint4*>(stg + off) = make_uint4(p[0], p[1], p[2], p[3]);
+                    }
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(1, 128);
+                if (leader) {
+                    tma_store_2d(&tmC, stg, n0 + c * 64, m0);
+                    tma_store_commit();
+                }
+                cbuf ^= 1;
+            }
+            // accumulator fully read: hand the TMEM stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+        if (leader) tma_store_wait_all<0>();
+    }
+    teardown(bars, tmem_cols, warp);
+}
+
+// =============================================================================
+// MN-major stream-K GEMM with fp32 reduction epilogue
+// =============================================================================
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    float* __restrict__ G, int ldg, int M, int N, int m_tiles, int n_tiles,
+                    int kb_total, int BN, uint32_t tmem_cols) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + kStages * kABytes;
+    Barriers* bars = (Barriers*)(sB + kStages * kBBytesMax);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+    }
+    setup(bars, tmem_cols, warp, lane);
+    const uint32_t tmem_base = bars->tmem_base;
+
+    // contiguous slice of the (tile, k-block) space owned by this CTA
+    const long long units = (long long)m_tiles * n_tiles * kb_total;
+    const long long u_begin = units * blockIdx.x / gridDim.x;
+    const long long u_end = units * (blockIdx.x + 1) / gridDim.x;
+    const int nb_boxes = (BN + 63) / 64;
+    const uint32_t b_bytes = (uint32_t)nb_boxes * 64 * BK * 2;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            long long u = u_begin;
+            while (u < u_end) {
+                const int tile = (int)(u / kb_total);
+                const int kb0 = (int)(u % kb_total);
+                const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+                const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
+                    uint8_t* a = sA + stage * kABytes;
+                    uint8_t* b = sB + stage * kBBytesMax;
+                    // boxes are {64 MN elements} x {64 k rows}: 8 KB each
+                    tma_load_2d(a, &tmA, &bars->full[stage], m0, kb * BK);
+                    tma_load_2d(a + 8192, &tmA, &bars->full[stage], m0 + 64, kb * BK);
+                    for (int x = 0; x < nb_boxes; ++x)
+                        tma_load_2d(b + x * 8192, &tmB, &bars->full[stage], n0 + x * 64, kb * BK);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                u += kb1 - kb0;
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = idesc_bf16(BM, BN, 1, 1);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            long long u = u_begin;
+            while (u < u_end) {
+                const int kb0 = (int)(u % kb_total);
+                const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a0 = smem_u32(sA + stage * kABytes);
+                    const uint32_t b0 = smem_u32(sB + stage * kBBytesMax);
+#pragma unroll
+                    for (int j = 0; j < BK / 16; ++j) {
+                        // MN-major: 64-element MN groups are 8 KB apart (LBO), 8-row k
+                        // groups 1 KB apart (SBO); one MMA consumes two k groups
+                        const uint64_t da = smem_desc_sw128(a0 + j * 2048, 8192, 1024);
+                        const uint64_t db = smem_desc_sw128(b0 + j * 2048, 8192, 1024);
+                        umma_bf16(d_tmem, da, db, idesc, (kb > kb0) || (j > 0));
+                    }
+                    umma_commit(&bars->empty[stage]);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&bars->tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                u += kb1 - kb0;
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        long long u = u_begin;
+        while (u < u_end) {
+            const int tile = (int)(u / kb_total);
+            const int kb0 = (int)(u % kb_total);
+            const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+            const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256);
+            const int h = m0 + q * 32 + lane;
+            float* grow = G + (size_t)h * ldg;
+            for (int c = 0; c < BN / 16; ++c) {
+                uint32_t v[16];
+                tmem_ld_32x16(t_row + (uint32_t)(c * 16), v);
+                tmem_ld_wait();
+                if (h < M) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const int d = n0 + c * 16 + g * 4;
+                        if (d + 3 < N) {
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(grow + d),
+                                         "f"(__uint_as_float(v[g * 4])), "f"(__uint_as_float(v[g * 4 + 1])),
+                                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
+                                         : "memory");
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                if (d + e < N) atomicAdd(grow + d + e, __uint_as_float(v[g * 4 + e]));
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+            u += kb1 - kb0;
+        }
+    }
+    teardown(bars, tmem_cols, warp);
+}
+
+// =============================================================================
+// host side: tensor maps and launches
+// =============================================================================
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+                cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+// 2-D bf16 tensor map: dims {inner, outer}, row pitch ld elements, 128-byte swizzle
+int make_map(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+             uint32_t box_inner, uint32_t box_outer) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        cme::set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return -2;
+    }
+    if (((uintptr_t)base & 15) || ((ld * 2) & 15)) {
+        cme::set_error("tensor map: base and row pitch must be 16-byte aligned (ld=%llu)",
+                       (unsigned long long)ld);
+        return -1;
+    }
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        cme::set_error("cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu "
+                       "box=%ux%u)", (int)r, (unsigned long long)inner, (unsigned long long)outer,
+                       (unsigned long long)ld, box_inner, box_outer);
+        return -3;
+    }
+    return 0;
+}
+
+uint32_t pow2_cols(int need) {
+    uint32_t c = 32;
+    while ((int)c < need) c <<= 1;
+    return c;
+}
+
+template <typename K>
+int opt_in_smem(K kernel, int bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, bool> done;  // per (kernel, device)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu);
+    auto key = std::make_pair((const void*)kernel, dev);
+    if (!done.count(key)) {
+        CME_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        done[key] = true;
+    }
+    return 0;
+}
+
+int launch_kmajor(int epi, const void* A, const void* B, void* Cout, int64_t M, int N, int K,
+                  int lda, int ldb, int ldc, cudaStream_t st) {
+    CME_CHECK_ARG(A && B && Cout && M > 0 && N > 0 && K > 0, "gemm_kmajor: bad argument");
+    CME_CHECK_ARG(N % 64 == 0, "gemm_kmajor: N (%d) must be a multiple of 64", N);
+    CME_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0 && lda >= K && ldb >= K && ldc >= N,
+                  "gemm_kmajor: leading dimensions must be multiples of 8 and cover the rows");
+    CME_CHECK_ARG(M < (1ll << 31), "gemm_kmajor: M too large");
+    const int BN = N >= 256 ? 256 : N;
+    const int m_tiles = (int)((M + BM - 1) / BM), n_tiles = (N + BN - 1) / BN;
+    CUtensorMap tmA, tmB, tmC;
+    int rc;
+    if ((rc = make_map(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM))) return rc;
+    if ((rc = make_map(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN))) return rc;
+    if ((rc = make_map(&tmC, Cout, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, BM))) return rc;
+    const uint32_t cols = pow2_cols(2 * BN);
+    const long long tiles = (long long)m_tiles * n_tiles;
+    const int grid = (int)std::min<long long>(tiles, cme::sm_count());
+    if (epi == 1) {
+        if ((rc = opt_in_smem(gemm_kmajor_kernel<1>, kSmemKMajor))) return rc;
+        gemm_kmajor_kernel<1><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
+                                                                  BN, cols);
+    } else {
+        if ((rc = opt_in_smem(gemm_kmajor_kernel<0>, kSmemKMajor))) return rc;
+        gemm_kmajor_kernel<0><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
+                                                                  BN, cols);
+    }
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cme_mlp_fwd1(const void* X, const void* W1c, const float* b1, void* A1, int64_t rows, int K,
+                 int H, int ldx, int ldh, void* stream) {
+    // b1 is folded into W1c (column K-1 of the augmented operands); the pointer
+    // is accepted for API symmetry and must be NULL
+    CME_CHECK_ARG(b1 == nullptr, "cme_mlp_fwd1: the bias lives in W1c's ones column; pass NULL");
+    const int Hp = (H + 63) / 64 * 64;
+    CME_CHECK_ARG(ldh >= Hp, "cme_mlp_fwd1: ldh (%d) must cover H rounded up to 64 (%d)", ldh, Hp);
+    return launch_kmajor(1, X, W1c, A1, rows, Hp, K, ldx, ldx, ldh, cme::as_stream(stream));
+}
+
+int cme_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int N, int K, int lda,
+                  int ldb, int ldc, void* stream) {
+    return launch_kmajor(0, A, B, Cout, M, N, K, lda, ldb, ldc, cme::as_stream(stream));
+}
+
+int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
+                int ldh, int ldg, void* stream) {
+    CME_CHECK_ARG(dZ1 && X && gW1 && rows > 0 && K > 0 && H > 0, "cme_mlp_dw1: bad argument");
+    CME_CHECK_ARG(ldx % 8 == 0 && ldh % 8 == 0 && ldg % 4 == 0 && ldx >= K && ldh >= H && ldg >= K,
+                  "cme_mlp_dw1: leading dimensions (ldx=%d ldh=%d ldg=%d)", ldx, ldh, ldg);
+    CME_CHECK_ARG(((uintptr_t)gW1 & 15) == 0, "cme_mlp_dw1: gW1 must be 16-byte aligned");
+    CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_dw1: too many rows");
+    // output tile: 128 rows of H  x  BN columns of K, BN a multiple of 16, <= 256
+    const int n_tiles = (K + 255) / 256;
+    const int BN = ((K + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    const int m_tiles = (H + BM - 1) / BM;
+    const int kb_total = (int)((rows + BK - 1) / BK);
+    CUtensorMap tmA, tmB;
+    int rc;
+    if ((rc = make_map(&tmA, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BK))) return rc;
+    if ((rc = make_map(&tmB, X, (uint64_t)K, (uint64_t)rows, (uint64_t)ldx, 64, BK))) return rc;
+    if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
+    const long long units = (long long)m_tiles * n_tiles * kb_total;
+    const int grid = (int)std::min<long long>(units, cme::sm_count());
+    gemm_mnmajor_kernel<<<grid, kThreads, kSmemMNMajor, cme::as_stream(stream)>>>(
+        tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+// hw2 q2 PageRank propagation (ref hw2code/pagerank.cu:9-28, 59-136).
+//
+// Differences from the reference kernel, all behaviour-preserving:
+//  * the per-edge product rank[e]*inv_deg[e] is formed once per node when the
+//    rank is written (contrib), so the random gather reads 4 bytes per edge
+//    instead of 8.  The product is the same fp32 multiply of the same operands,
+//    so the sum sees bit-identical terms in the same order.
+//  * 64-bit row offsets (N*avg_edges passes 2^32 for the 64 M-node target).
+//  * rows [row_begin,row_end) only, and the new contrib slice is stored to
+//    every rank's buffer from inside the kernel: the rank-vector all-gather of
+//    a row-partitioned multi-GPU run is fused into the SpMV (peer stores ride
+//    NVLink while other rows are still gathering).
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) prescale_kernel(const float* __restrict__ rank,
+                                                       const float* __restrict__ inv_deg,
+                                                       float* __restrict__ contrib, int64_t n) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        contrib[i] = rank[i] * inv_deg[i];
+}
+
+template <int MAX_PEERS>
+struct PeerList {
+    float* p[MAX_PEERS];
+};
+
+__global__ void __launch_bounds__(256)
+propagate_kernel(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict__ edges,
+                 const float* __restrict__ contrib_in, const float* __restrict__ inv_deg,
+                 float* __restrict__ rank_out, float* __restrict__ contrib_out,
+                 float* const* __restrict__ peer_contrib, int nranks, int64_t row_begin,
+                 int64_t row_end, float base) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = row_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_end;
+         i += stride) {
+        int64_t j = row_ptr[i];
+        const int64_t end = row_ptr[i + 1];
+        float sum = 0.f;
+        // four gathers in flight, accumulated in edge order
+        for (; j + 4 <= end; j += 4) {
+            const uint32_t e0 = edges[j], e1 = edges[j + 1], e2 = edges[j + 2], e3 = edges[j + 3];
+            const float c0 = __ldg(contrib_in + e0), c1 = __ldg(contrib_in + e1);
+            const float c2 = __ldg(contrib_in + e2), c3 = __ldg(contrib_in + e3);
+            sum += c0;
+            sum += c1;
+            sum += c2;
+            sum += c3;
+        }
+        for (; j < end; ++j) sum += __ldg(contrib_in + edges[j]);
+        const float r = base + 0.5f * sum;
+        rank_out[i] = r;
+        const float c = r * inv_deg[i];
+        if (nranks <= 1) {
+            contrib_out[i] = c;
+        } else {
+            for (int p = 0; p < nranks; ++p) peer_contrib[p][i] = c;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+gen_edges_kernel(uint32_t* __restrict__ edges, int64_t begin, int64_t count, uint64_t n,
+                 uint64_t seed) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < count; k += stride) {
+        const int64_t j = begin + k;
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(j + 1);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        edges[k] = (uint32_t)(z % n);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int cme_pagerank_prescale(const float* rank, const float* inv_deg, float* contrib, int64_t n,
+                          void* stream) {
+    CME_CHECK_ARG(rank && inv_deg && contrib && n > 0, "cme_pagerank_prescale: bad argument");
+    prescale_kernel<<<cme::stride_grid(n, 256, 8), 256, 0, cme::as_stream(stream)>>>(rank, inv_deg,
+                                                                                    contrib, n);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_pagerank_step(const int64_t* row_ptr, const uint32_t* edges, const float* contrib_in,
+                      const float* inv_deg, float* rank_out, float* contrib_out,
+                      float* const* peer_contrib, int nranks, int64_t row_begin, int64_t row_end,
+                      int64_t num_nodes, void* stream) {
+    CME_CHECK_ARG(row_ptr && edges && contrib_in && inv_deg && rank_out,
+                  "cme_pagerank_step: null buffer");
+    CME_CHECK_ARG(0 <= row_begin && row_begin <= row_end && row_end <= num_nodes,
+                  "cme_pagerank_step: bad row range");
+    CME_CHECK_ARG(nranks <= 1 ? contrib_out != nullptr : peer_contrib != nullptr,
+                  "cme_pagerank_step: missing contrib destination");
+    if (row_end == row_begin) return 0;
+    const float base = 0.5f / (float)num_nodes;
+    const int grid = cme::stride_grid(row_end - row_begin, 256, 8, 8);
+    propagate_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
+        row_ptr, edges, contrib_in, inv_deg, rank_out, contrib_out, peer_contrib, nranks,
+        row_begin, row_end, base);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_pagerank_gen_edges(uint32_t* edges, int64_t edge_begin, int64_t edge_count,
+                           int64_t num_nodes, uint64_t seed, void* stream) {
+    CME_CHECK_ARG(edges && edge_count >= 0 && num_nodes > 0, "cme_pagerank_gen_edges: bad argument");
+    if (edge_count == 0) return 0;
+    gen_edges_kernel<<<cme::stride_grid(edge_count, 256, 8), 256, 0, cme::as_stream(stream)>>>(
+        edges, edge_begin, edge_count, (uint64_t)num_nodes, seed);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

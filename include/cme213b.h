@@ -1,0 +1,209 @@
+/*
+ * cme213b device library (libcme213b.so): hand-written sm_100a kernels behind a
+ * plain C ABI.  Pointers are device pointers unless a parameter says "host".
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *
+ * Return value: 0 on success, a positive cudaError_t value on a CUDA failure,
+ * a negative value on a rejected argument.  cme_last_error() returns a
+ * thread-local message for the last non-zero return.
+ *
+ * Nothing here synchronises the device unless the comment says so.
+ * Reference behaviour is cited as file:line relative to the reference tree.
+ */
+#ifndef CME213B_H_
+#define CME213B_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* cme_last_error(void);
+int cme_version(void);
+/* sm_count / cc_major / cc_minor of the current device (any may be NULL). */
+int cme_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- hw2 q1: byte shift (ref hw2code/shift.cu:13-99) -----------------------
+ * out[i] = in[i] + shift (mod 256) for i < n.  variant: 0 = one byte per thread
+ * step, 1 = 32-bit words, 2 = 64-bit words, 3 = 128-bit vectors (the B200
+ * path).  Packed variants use per-byte SIMD adds, so bytes never carry into
+ * their neighbours (the reference's plain 32-bit add did, ref shift.cu:29).
+ * in/out must be 16-byte aligned for variants 1-3; the tail is handled. */
+int cme_shift_bytes(const uint8_t* in, uint8_t* out, size_t n, uint8_t shift, int variant,
+                    void* stream);
+
+/* ---- hw2 q2: PageRank (ref hw2code/pagerank.cu:9-136) ----------------------
+ * One propagation step over rows [row_begin,row_end) of a CSR graph:
+ *   rank_out[i] = 0.5/N + 0.5 * sum_j contrib_in[edges[j]]
+ * with contrib = rank*inv_deg precomputed per node (bitwise the same products
+ * the reference forms per edge).  Also writes contrib_out[i] = rank_out[i] *
+ * inv_deg[i] for the next step.  If nranks > 1, peer_contrib is a DEVICE array
+ * of nranks pointers to every rank's contrib_out buffer (peer-mapped) and the
+ * slice is stored to all of them (the rank all-gather fused into the SpMV). */
+int cme_pagerank_prescale(const float* rank, const float* inv_deg, float* contrib, int64_t n,
+                          void* stream);
+int cme_pagerank_step(const int64_t* row_ptr, const uint32_t* edges, const float* contrib_in,
+                      const float* inv_deg, float* rank_out, float* contrib_out,
+                      float* const* peer_contrib, int nranks, int64_t row_begin, int64_t row_end,
+                      int64_t num_nodes, void* stream);
+/* Device-side graph generator matching cmeh_pagerank_graph (same splitmix64). */
+int cme_pagerank_gen_edges(uint32_t* edges, int64_t edge_begin, int64_t edge_count,
+                           int64_t num_nodes, uint64_t seed, void* stream);
+
+/* ---- hw3: 2-D heat diffusion (ref hw3code/gpuStencil.cu, hw3code/BC.h) -----
+ * Grids are gx*gy floats, border b = order/2.  One call = one time step on
+ * rows [y_begin,y_end) of the interior (0-based interior row index), which is
+ * how a row-slab of a multi-GPU decomposition is expressed; a single GPU
+ * passes 0, ny.  variant: 0 = one point per thread (ref gpuStencil),
+ * 1 = several rows per thread (ref gpuStencilLoop), 2 = shared-memory tile
+ * with halo (what the reference left as a stub, ref gpuStencil.cu:263-308).
+ * bc: if non-zero the same launch also writes next.border = curr.border *
+ * bc_scale (ref BC.h:7-38) for the border cells adjacent to the rows it owns. */
+int cme_heat_step(float* next, const float* curr, int gx, int gy, int order, float xcfl,
+                  float ycfl, int variant, int bc, float bc_scale, void* stream);
+int cme_heat_bc(float* next, const float* curr, int gx, int gy, int order, float bc_scale,
+                void* stream);
+/* Slab step for domain decomposition along y.  The local grid holds
+ * rows_local interior rows plus b ghost rows above and below.  After computing,
+ * the kernel's edge blocks store the first/last b computed rows straight into
+ * the neighbours' ghost rows (peer-mapped pointers, may be NULL at the domain
+ * ends) -- the halo exchange fused into the sweep.  Physical top/bottom border
+ * rows (ranks at the ends) and the left/right border columns get the BC decay. */
+int cme_heat_slab_step(float* next, const float* curr, float* up_next_ghost,
+                       float* down_next_ghost, int gx, int rows_local, int order, float xcfl,
+                       float ycfl, float bc_scale, int is_top, int is_bottom, void* stream);
+
+/* ---- hw4: cipher primitives (ref hw4code/create_cipher.cu, solve_cipher.cu) */
+/* Lower-case A-Z, drop everything that is not a letter; *out_count (device
+ * int64) receives the number of bytes kept.  Stable. scratch: >= 4*(n/2048+2)
+ * +16 bytes of device memory. */
+int cme_sanitize_compact(const uint8_t* in, size_t n, uint8_t* out, int64_t* out_count,
+                         void* scratch, size_t scratch_bytes, void* stream);
+/* counts[256] (device uint64, zeroed by the call) of text[offset + k*stride]. */
+int cme_byte_histogram(const uint8_t* text, size_t n, size_t stride, size_t offset,
+                       unsigned long long* counts, void* stream);
+/* All key positions at once: counts[period][256]. */
+int cme_strided_histograms(const uint8_t* text, size_t n, int period,
+                           unsigned long long* counts, void* stream);
+/* out[i] = text[i] + shifts[i % period] as unsigned char, no mod-26 wrap
+ * (ref create_cipher.cu:58-61); wrap26 != 0 keeps letters inside a-z. */
+int cme_vigenere_shift(const uint8_t* text, uint8_t* out, size_t n, const int32_t* shifts,
+                       int period, int wrap26, void* stream);
+/* matches[k] = #{i : text[i] == text[i + lag0 + k]}, k < num_lags
+ * (ref solve_cipher.cu:83-88, many lags per launch). */
+int cme_lag_match_counts(const uint8_t* text, size_t n, int lag0, int num_lags,
+                         unsigned long long* matches, void* stream);
+
+/* ---- hw1 on the GPU: parity sums and LSD radix sort ------------------------ */
+int cme_parity_sum(const uint32_t* v, size_t n, unsigned long long* out2, void* stream);
+/* 4 passes of 8 bits; tmp = n keys, scratch >= cme_radix_scratch_bytes(n). */
+size_t cme_radix_scratch_bytes(size_t n);
+int cme_radix_sort(uint32_t* keys, uint32_t* tmp, size_t n, void* scratch, size_t scratch_bytes,
+                   void* stream);
+
+/* ---- fp64 parity path (ref fpcode/gpu_func.cu) -----------------------------
+ * Column-major C = alpha*op(A)*op(B) + beta*C, the reference's myGEMM contract
+ * (ref gpu_func.cu:259-297) with both transposes allowed.  M,N,K are the
+ * dimensions of op(A) (MxK), op(B) (KxN), C (MxN); lda/ldb/ldc leading dims. */
+int cme_dgemm(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
+              const double* B, int ldb, double beta, double* C, int ldc, void* stream);
+/* Fused fp64 MLP pieces, column-major like the reference's device_cache.
+ * z is rows x cols (one sample per column). */
+int cme_d_bias_sigmoid(double* z, const double* bias, int rows, int cols, void* stream);
+/* In place: z <- softmax(z + bias) per column (max-subtracted); then
+ * diff = (softmax - onehot(label)) * scale; loss_sum += -log p[label] (may be NULL). */
+int cme_d_bias_softmax_ce(double* z, const double* bias, const int32_t* labels, double* diff,
+                          double scale, double* loss_sum, int rows, int cols, void* stream);
+/* dz = da * a * (1-a) elementwise. */
+int cme_d_dsigmoid(const double* da, const double* a, double* dz, size_t n, void* stream);
+/* out[r] = sum_c m[r + c*rows]  (ref gpu_func.cu:359-382). */
+int cme_d_row_sum(const double* m, double* out, int rows, int cols, void* stream);
+/* p -= lr * (g + reg * p) for n values (reg = 0 for biases). */
+int cme_d_sgd(double* p, const double* g, size_t n, double lr, double reg, void* stream);
+int cme_d_axpby(double* c, const double* a, const double* b, double alpha, double beta, size_t n,
+                void* stream);
+
+/* ---- bf16 tensor-core path --------------------------------------------------
+ * Row-major activations: X[B][ldx] bf16, A1[B][ldh] bf16, compute weights
+ * W1c[Hp][ldx] bf16 (K-major for tcgen05), W2[C][H] fp32.  ldx, ldh are
+ * multiples of 64 elements, Hp = H rounded up to 64.  The bias b1 is folded
+ * into the GEMMs: X carries a column of ones at index K-1 and W1c carries b1
+ * there, so K below is "pixels + 1" (785 for MNIST). */
+
+/* Minibatch staging: uint8 pixels (rows x cols, dense) -> bf16 rows with leading
+ * dimension ld; if add_ones, column `cols` is set to 1.0; remaining pad columns
+ * are zeroed.  src may be a peer-mapped pointer into another GPU's memory: each
+ * rank pulls its slice of the minibatch from the owner over NVLink, which
+ * replaces the host MPI_Scatter (ref fpcode/neural_network.cpp:460-481). */
+int cme_u8_to_bf16_rows(const uint8_t* src, void* dst_bf16, int64_t rows, int cols, int ld,
+                        int add_ones, void* stream);
+
+/* tcgen05 GEMM #1:  A1 = sigmoid(X * W1c^T), bf16 out through TMA stores, fp32
+ * accumulate in TMEM.  X: rows x K, W1c: Hp x K (pad rows zero), A1: rows x Hp.
+ * b1 must be NULL (the bias is inside W1c).  Replaces ref gpu_func.cu K1+K8+K6
+ * (sGEMM_kernel :92-147, gpuMatVecSum :385-408, gpuSigmoid :332-356). */
+int cme_mlp_fwd1(const void* X, const void* W1c, const float* b1, void* A1, int64_t rows, int K,
+                 int H, int ldx, int ldh, void* stream);
+/* Plain bf16 GEMM on the same kernel: C[M,N] = A[M,K] * B[N,K]^T (N % 64 == 0).
+ * Used by the GEMM benchmark against cuBLAS (ref fpcode/utils/tests.cpp:126-280). */
+int cme_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int N, int K, int lda, int ldb,
+                  int ldc, void* stream);
+/* Layer 2 + softmax + cross-entropy gradient in one pass over A1:
+ * dz2[r][c] = (softmax(A1[r]*W2^T + b2)[c] - [c==label[r]]) * scale as fp32 rows
+ * of 16; loss_sum (may be NULL) += -log p[label]; pred (may be NULL) = argmax;
+ * gb2 (may be NULL) += column sums of dz2.  Replaces K1(fwd2)+K8+K5+K9+K7(db2). */
+int cme_mlp_fwd2_softmax(const void* A1, const float* W2, const float* b2, const int32_t* labels,
+                         float* dz2, float* loss_sum, int32_t* pred, float* gb2, float scale,
+                         int64_t rows, int H, int ldh, int C, void* stream);
+/* Backward elementwise + dW2 in one pass over A1:
+ * dZ1[r][h] = (sum_c dz2[r][c]*W2[c][h]) * a*(1-a) (bf16 out),
+ * gW2[c][h] += sum_r dz2[r][c]*A1[r][h].  Replaces K2+K10+K3(dW2).  gW2 must be
+ * zeroed by the caller. */
+int cme_mlp_bwd_elem(const void* A1, const float* dz2, const float* W2, void* dZ1, float* gW2,
+                     int64_t rows, int H, int ldh, int C, void* stream);
+/* tcgen05 GEMM #2: gW1[h][k] += sum_r dZ1[r][h] * X[r][k]  (fp32 reductions into
+ * gW1, H x K with ld = ldg), both operands MN-major, stream-K balanced over all
+ * SMs.  Column K-1 (the ones column) receives the b1 gradient.  Replaces K3
+ * (sGEMM_BT_kernel :205-256) for dW1 and K7 for db1.  gW1 must be zeroed first. */
+int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
+                int ldh, int ldg, void* stream);
+
+/* Flat fp32 parameter / gradient vector of the bf16 trainer:
+ *   [ W1aug (Hp x ldx, b1 in column K-1) | W2 (C x H) | b2 (C) ]  each segment
+ * padded to a multiple of 4 floats.
+ * Fused all-reduce + L2 + SGD + bf16 re-cast.  Rank r owns the r-th 1/nranks
+ * slice: it sums that slice of every rank's gradient buffer straight from peer
+ * memory (fixed rank order), applies  p -= lr * (sum_g + reg * p)  (reg only on
+ * W1 columns < kreg and on [w2_begin, w2_end)) and stores the new fp32 value
+ * into every rank's parameter replica plus, for the W1 part, the bf16 value
+ * into every rank's W1c.  Replaces the four MPI_Allreduce calls and the host
+ * SGD (ref fpcode/neural_network.cpp:501-541).  grads/params/w1c are HOST
+ * arrays of nranks peer-mapped device pointers.  The caller orders ranks with
+ * cme_peer_barrier before (gradients complete) and after (weights visible). */
+int cme_allreduce_sgd(float* const* grads, float* const* params, void* const* w1c, int rank,
+                      int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
+                      int64_t w2_begin, int64_t w2_end, float lr, float reg, void* stream);
+/* Same update through the NVSwitch multicast mapping: multimem.ld_reduce sums in
+ * the switch, multimem.st replicates the result to all GPUs. */
+int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_params,
+                         void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
+                         int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
+                         void* stream);
+
+/* Cross-GPU flag barrier over a peer-mapped pad of uint32 slots.  pads: DEVICE
+ * array of nranks pointers (one pad per rank, >= 8*64 slots, zero-initialised).
+ * Slot layout pads[dst][channel*64 + src].  do_signal: bump my slot on every
+ * peer (release); do_wait: spin until every peer's slot on my pad has reached
+ * `epoch` (acquire).  `epoch` counts barriers on that channel, starting at 1.
+ * One rank per GPU only: ranks spinning on each other must not share a GPU. */
+int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, uint32_t epoch,
+                     int do_signal, int do_wait, void* stream);
+/* P2P copy bandwidth probe: dst (local) <- src (peer), 128-bit loads. */
+int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CME213B_H_ */
