@@ -1,0 +1,243 @@
+"""Device engines of the MLP: the bf16 tensor-core engine and the fp64 parity engine.
+
+An engine owns every device buffer of one rank for a fixed maximum local batch (the
+reference's `device_cache`, ref fpcode/inc/gpu_func.h:49-101, without its unused Z1/Z2 and
+without re-uploading weights every step) and exposes `step()`: forward,
+backward, gradient all-reduce and SGD for one minibatch slice, all on the device.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from ..ops import device as dev
+from ..parallel.dist import DistInfo, SymmetricTensor
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class MLPEngineBF16:
+    """bf16 operands / fp32 accumulate on tcgen05, fp32 master weights.
+
+    Layout of the flat fp32 parameter and gradient vectors:
+        [ W1aug (Hp x ldx; columns 0..D-1 weights, column D = b1, rest 0) | W2 (C x H) | b2 (C) ]
+    `w1c` is the bf16 compute copy of W1aug that the forward GEMM reads (K-major).  With more
+    than one rank all three live in symmetric memory: the fused all-reduce + SGD kernel reads
+    every rank's gradients and writes every rank's weights through peer pointers."""
+
+    def __init__(self, H, max_rows: int, info: DistInfo | None = None, comm: str = "fused"):
+        self.info = info or DistInfo(device=torch.device("cuda", torch.cuda.current_device()))
+        self.D, self.Hh, self.C = H
+        if self.C != 10:
+            raise ValueError("the bf16 engine is built for 10 classes")
+        self.K = self.D + 1                       # pixels + the ones column that carries b1
+        self.ldx = _round_up(self.K, 64)
+        self.Hp = _round_up(self.Hh, 64)
+        self.ldh = self.Hp
+        self.max_rows = max_rows
+        self.comm = comm if self.info.world > 1 else "local"
+        r4 = lambda v: _round_up(v, 4)            # noqa: E731
+        self.n_w1 = self.Hp * self.ldx
+        self.o_w2 = self.n_w1
+        self.o_b2 = self.o_w2 + r4(self.C * self.Hh)
+        self.n_total = self.o_b2 + r4(self.C)
+        d = self.info.device
+        self.params = SymmetricTensor(self.n_total, torch.float32, self.info)
+        self.grads = SymmetricTensor(self.n_total, torch.float32, self.info)
+        self.w1c = SymmetricTensor(self.n_w1, torch.bfloat16, self.info)
+        self.pads = SymmetricTensor(1024, torch.int32, self.info)
+        self.pads_dev = self.pads.ptr_table_dev()
+        self.xb = torch.zeros((max_rows, self.ldx), dtype=torch.bfloat16, device=d)
+        self.a1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
+        self.dz1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
+        self.dz2 = torch.zeros((max_rows, 16), dtype=torch.float32, device=d)
+        self.pred = torch.zeros(max_rows, dtype=torch.int32, device=d)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=d)
+        self.use_mc = False
+        if self.info.world > 1:
+            dist.barrier()                        # every rank's buffers are zeroed before use
+
+    # ---- views into the flat vectors ----
+    def _views(self, flat: torch.Tensor):
+        w1 = flat[: self.n_w1].view(self.Hp, self.ldx)
+        w2 = flat[self.o_w2: self.o_w2 + self.C * self.Hh].view(self.C, self.Hh)
+        b2 = flat[self.o_b2: self.o_b2 + self.C]
+        return w1, w2, b2
+
+    def load_params(self, nn) -> None:
+        """Host model (reference layout W[i] = [H_out, H_in] fp64) -> device buffers."""
+        w1, w2, b2 = self._views(self.params.tensor)
+        w1.zero_()
+        w1[: self.Hh, : self.D] = nn.W[0].to(w1.device, torch.float32)
+        w1[: self.Hh, self.D] = nn.b[0].to(w1.device, torch.float32)
+        w2.copy_(nn.W[1].to(w2.device, torch.float32))
+        b2.copy_(nn.b[1].to(b2.device, torch.float32))
+        self.w1c.tensor.copy_(self.params.tensor[: self.n_w1].to(torch.bfloat16))
+        torch.cuda.synchronize()
+        if self.info.world > 1:
+            dist.barrier()
+
+    def store_params(self, nn) -> None:
+        torch.cuda.synchronize()
+        w1, w2, b2 = self._views(self.params.tensor)
+        nn.W[0] = w1[: self.Hh, : self.D].double().cpu().contiguous()
+        nn.b[0] = w1[: self.Hh, self.D].double().cpu().contiguous()
+        nn.W[1] = w2.double().cpu().contiguous()
+        nn.b[1] = b2.double().cpu().contiguous()
+
+    # ---- one minibatch slice ----
+    def stage(self, x_u8_ptr: int, rows: int) -> None:
+        """uint8 pixels at x_u8_ptr (local or peer-mapped) -> bf16 rows + ones column."""
+        dev.u8_to_bf16_rows(x_u8_ptr, self.xb, rows, self.D, add_ones=True)
+
+    def forward(self, rows: int, labels: torch.Tensor | None, scale: float, want_loss: bool = False,
+                want_grad: bool = True) -> None:
+        _, w2, b2 = self._views(self.params.tensor)
+        _, _, gb2 = self._views(self.grads.tensor)
+        dev.mlp_fwd1(self.xb, self.w1c.tensor, self.a1, rows, self.K, self.Hh)
+        dev.mlp_fwd2_softmax(self.a1, w2, b2, labels, self.dz2 if want_grad else None,
+                             self.loss if want_loss else None, self.pred,
+                             gb2 if want_grad else None, scale, rows, self.Hh, self.C)
+
+    def backward(self, rows: int) -> None:
+        _, w2, _ = self._views(self.params.tensor)
+        gw1, gw2, _ = self._views(self.grads.tensor)
+        dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, gw2, rows, self.Hh, self.C)
+        dev.mlp_dw1(self.dz1, self.xb, gw1, rows, self.K, self.Hh, self.ldx)
+
+    def update(self, lr: float, reg: float) -> None:
+        """Gradient all-reduce + L2 + SGD + bf16 re-cast (ref fpcode/neural_network.cpp:501-541)."""
+        info = self.info
+        w2_begin, w2_end = self.o_w2, self.o_w2 + self.C * self.Hh
+        if self.comm == "nccl":
+            # baseline path: library all-reduce, then the same update kernel on local pointers
+            dist.all_reduce(self.grads.tensor)
+            dev.allreduce_sgd([self.grads.tensor.data_ptr()], [self.params.tensor.data_ptr()],
+                              [self.w1c.tensor.data_ptr()], 0, self.n_total, self.n_w1, self.ldx,
+                              self.D, w2_begin, w2_end, lr, reg)
+            return
+        if info.world > 1:
+            dev.peer_barrier(self.pads_dev, info.rank, info.world, 0, 0)   # all gradients complete
+        if self.use_mc and self.grads.multicast_ptr:
+            dev.allreduce_sgd_mc(self.grads.multicast_ptr, self.params.tensor.data_ptr(),
+                                 self.params.multicast_ptr, self.w1c.multicast_ptr, info.rank,
+                                 info.world, self.n_total, self.n_w1, self.ldx, self.D, w2_begin,
+                                 w2_end, lr, reg)
+        else:
+            dev.allreduce_sgd(self.grads.peer_ptrs, self.params.peer_ptrs, self.w1c.peer_ptrs,
+                              info.rank, self.n_total, self.n_w1, self.ldx, self.D, w2_begin, w2_end,
+                              lr, reg)
+        if info.world > 1:
+            dev.peer_barrier(self.pads_dev, info.rank, info.world, 1, 0)   # all weights visible
+
+    def step(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
+             norm: float, want_loss: bool = False) -> None:
+        """One training step on `rows` local samples; `norm` = global sample count of the
+        minibatch (in_proc * P, ref fpcode/neural_network.cpp:330-334)."""
+        if rows > self.max_rows:
+            raise ValueError(f"step: {rows} rows exceed the engine capacity {self.max_rows}")
+        self.stage(x_u8_ptr, rows)
+        self.grads.tensor.zero_()
+        self.forward(rows, labels, 1.0 / norm, want_loss=want_loss)
+        self.backward(rows)
+        self.update(lr, reg)
+
+    def predict(self, x_u8: torch.Tensor) -> torch.Tensor:
+        """Arg-max classes for [n, D] uint8 images on the device (chunks of max_rows)."""
+        out = torch.empty(x_u8.shape[0], dtype=torch.int32, device=self.info.device)
+        for lo in range(0, x_u8.shape[0], self.max_rows):
+            hi = min(x_u8.shape[0], lo + self.max_rows)
+            chunk = x_u8[lo:hi].contiguous().to(self.info.device)
+            self.stage(chunk.data_ptr(), hi - lo)
+            self.forward(hi - lo, None, 0.0, want_grad=False)
+            out[lo:hi] = self.pred[: hi - lo]
+        return out
+
+
+class MLPEngineFP64:
+    """fp64 parity engine on this repo's SIMT kernels (grade modes, 1e-7 vs the serial run).
+
+    Buffers are column-major like the reference's device_cache; a column-major M x N matrix is
+    held as a contiguous torch tensor of shape [N, M]."""
+
+    def __init__(self, H, max_rows: int, info: DistInfo | None = None):
+        self.info = info or DistInfo(device=torch.device("cuda", torch.cuda.current_device()))
+        self.D, self.Hh, self.C = H
+        self.max_rows = max_rows
+        d, f = self.info.device, torch.float64
+        D, Hh, C = self.D, self.Hh, self.C
+        self.sizes = [Hh * D, Hh, C * Hh, C]
+        self.offs = [0, Hh * D, Hh * D + Hh, Hh * D + Hh + C * Hh]
+        n = sum(self.sizes)
+        self.params = torch.zeros(n, dtype=f, device=d)
+        self.grads = torch.zeros(n, dtype=f, device=d)
+        self.x = torch.zeros((max_rows, D), dtype=f, device=d)
+        self.a1 = torch.zeros((max_rows, Hh), dtype=f, device=d)
+        self.da1 = torch.zeros((max_rows, Hh), dtype=f, device=d)
+        self.dz1 = torch.zeros((max_rows, Hh), dtype=f, device=d)
+        self.z2 = torch.zeros((max_rows, C), dtype=f, device=d)
+        self.diff = torch.zeros((max_rows, C), dtype=f, device=d)
+        self.loss = torch.zeros(1, dtype=f, device=d)
+
+    def _seg(self, flat, i):
+        return flat[self.offs[i]: self.offs[i] + self.sizes[i]]
+
+    def load_params(self, nn) -> None:
+        d = self.info.device
+        # column-major H x D == contiguous [D, H] == W.T
+        self._seg(self.params, 0).copy_(nn.W[0].T.contiguous().view(-1).to(d))
+        self._seg(self.params, 1).copy_(nn.b[0].to(d))
+        self._seg(self.params, 2).copy_(nn.W[1].T.contiguous().view(-1).to(d))
+        self._seg(self.params, 3).copy_(nn.b[1].to(d))
+
+    def store_params(self, nn) -> None:
+        torch.cuda.synchronize()
+        D, Hh, C = self.D, self.Hh, self.C
+        nn.W[0] = self._seg(self.params, 0).view(D, Hh).T.contiguous().cpu()
+        nn.b[0] = self._seg(self.params, 1).clone().cpu()
+        nn.W[1] = self._seg(self.params, 2).view(Hh, C).T.contiguous().cpu()
+        nn.b[1] = self._seg(self.params, 3).clone().cpu()
+
+    def forward(self, rows: int, labels: torch.Tensor | None, scale: float, want_loss=False) -> None:
+        D, Hh, C = self.D, self.Hh, self.C
+        W1, b1, W2, b2 = (self._seg(self.params, i) for i in range(4))
+        dev.dgemm(False, False, Hh, rows, D, 1.0, W1, Hh, self.x, D, 0.0, self.a1, Hh)
+        dev.d_bias_sigmoid(self.a1, b1, Hh, rows)
+        dev.dgemm(False, False, C, rows, Hh, 1.0, W2, C, self.a1, Hh, 0.0, self.z2, C)
+        dev.d_bias_softmax_ce(self.z2, b2, labels, self.diff if labels is not None else None, scale,
+                              self.loss if want_loss else None, C, rows)
+
+    def backward(self, rows: int) -> None:
+        D, Hh, C = self.D, self.Hh, self.C
+        W2 = self._seg(self.params, 2)
+        gW1, gb1, gW2, gb2 = (self._seg(self.grads, i) for i in range(4))
+        dev.dgemm(False, True, C, Hh, rows, 1.0, self.diff, C, self.a1, Hh, 0.0, gW2, C)
+        dev.d_row_sum(self.diff, gb2, C, rows)
+        dev.dgemm(True, False, Hh, rows, C, 1.0, W2, C, self.diff, C, 0.0, self.da1, Hh)
+        dev.d_dsigmoid(self.da1[:rows], self.a1[:rows], self.dz1)
+        dev.dgemm(False, True, Hh, D, rows, 1.0, self.dz1, Hh, self.x, D, 0.0, gW1, Hh)
+        dev.d_row_sum(self.dz1, gb1, Hh, rows)
+
+    def update(self, lr: float, reg: float) -> None:
+        if self.info.world > 1:
+            dist.all_reduce(self.grads)             # parity path: library all-reduce
+        for i, r in ((0, reg), (1, 0.0), (2, reg), (3, 0.0)):
+            dev.d_sgd(self._seg(self.params, i), self._seg(self.grads, i), lr, r)
+
+    def step(self, x: torch.Tensor, labels: torch.Tensor, rows: int, lr: float, reg: float,
+             norm: float, want_loss: bool = False) -> None:
+        self.x[:rows].copy_(x[:rows])
+        self.forward(rows, labels, 1.0 / norm, want_loss=want_loss)
+        self.backward(rows)
+        self.update(lr, reg)
+
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        out = torch.empty(x.shape[0], dtype=torch.int64, device=self.info.device)
+        for lo in range(0, x.shape[0], self.max_rows):
+            hi = min(x.shape[0], lo + self.max_rows)
+            self.x[: hi - lo].copy_(x[lo:hi].to(self.info.device, torch.float64))
+            self.forward(hi - lo, None, 0.0)
+            out[lo:hi] = self.z2[: hi - lo].argmax(dim=1)
+        return out

@@ -105,9 +105,23 @@ allreduce_sgd_mc_kernel(const float* __restrict__ mc_grads, float* __restrict__ 
     }
 }
 
-// signal every peer, then wait until every peer has signalled `epoch` times
+// signal every peer, then wait until every peer has signalled `epoch` times.
+// epoch == 0: use (and advance) the device-side call counter kept in slot 63 of
+// this rank's own channel row, so the launch has no per-call host argument and
+// can be captured in a CUDA graph.
 __global__ void peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank, int nranks,
                                     int channel, uint32_t epoch, int do_signal, int do_wait) {
+    __shared__ uint32_t target;
+    if (threadIdx.x == 0) {
+        uint32_t e = epoch;
+        if (e == 0) {
+            uint32_t* counter = pads[rank] + channel * 64 + 63;
+            e = *counter + 1;
+            *counter = e;
+        }
+        target = e;
+    }
+    __syncthreads();
     const int r = threadIdx.x;
     if (r >= nranks) return;
     if (do_signal) {
@@ -117,10 +131,11 @@ __global__ void peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank
     }
     if (do_wait) {
         const uint32_t* mine = pads[rank] + channel * 64 + r;
+        const uint32_t want = target;
         uint32_t v;
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-        } while ((int32_t)(v - epoch) < 0);
+        } while ((int32_t)(v - want) < 0);
     }
 }
 

@@ -53,10 +53,8 @@ int cme_pagerank_gen_edges(uint32_t* edges, int64_t edge_begin, int64_t edge_cou
                            int64_t num_nodes, uint64_t seed, void* stream);
 
 /* ---- hw3: 2-D heat diffusion (ref hw3code/gpuStencil.cu, hw3code/BC.h) -----
- * Grids are gx*gy floats, border b = order/2.  One call = one time step on
- * rows [y_begin,y_end) of the interior (0-based interior row index), which is
- * how a row-slab of a multi-GPU decomposition is expressed; a single GPU
- * passes 0, ny.  variant: 0 = one point per thread (ref gpuStencil),
+ * Grids are gx*gy floats, border b = order/2.  One call = one time step of the
+ * whole interior.  variant: 0 = one point per thread (ref gpuStencil),
  * 1 = several rows per thread (ref gpuStencilLoop), 2 = shared-memory tile
  * with halo (what the reference left as a stub, ref gpuStencil.cu:263-308).
  * bc: if non-zero the same launch also writes next.border = curr.border *
@@ -196,7 +194,11 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
  * array of nranks pointers (one pad per rank, >= 8*64 slots, zero-initialised).
  * Slot layout pads[dst][channel*64 + src].  do_signal: bump my slot on every
  * peer (release); do_wait: spin until every peer's slot on my pad has reached
- * `epoch` (acquire).  `epoch` counts barriers on that channel, starting at 1.
+ * `epoch` (acquire).  `epoch` counts barriers on that channel, starting at 1;
+ * epoch == 0 means "use and advance the device-side counter in slot 63 of my own
+ * channel row", which keeps the launch free of per-call host arguments (CUDA graphs).
+ * A channel must be used either always with signal+wait together or split
+ * consistently, so that every rank signals exactly once per epoch.
  * One rank per GPU only: ranks spinning on each other must not share a GPU. */
 int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, uint32_t epoch,
                      int do_signal, int do_wait, void* stream);

@@ -1,0 +1,7 @@
+set -x
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -q -m gpu --timeout 300 2>&1 | tail -30
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5
+timeout 600 python bench.py --steps 10 --warmup 3 2>&1 | tail -5 | tee gpurun_out/bench_wide_1.log
+timeout 600 python bench.py --config small --steps 50 --warmup 5 2>&1 | tail -5 | tee gpurun_out/bench_small_1.log

@@ -1,0 +1,141 @@
+"""GPU engines of the MLP against the fp64 CPU oracle."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+from cme213_sp18_b200.models import mlp as M
+from cme213_sp18_b200.utils import grading, mnist
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _info():
+    from cme213_sp18_b200.parallel.dist import DistInfo
+
+    return DistInfo(device=torch.device("cuda", 0))
+
+
+@pytest.mark.parametrize("H,rows", [([784, 100, 10], 800), ([784, 1000, 10], 333), ([50, 64, 10], 64)])
+def test_bf16_single_step_matches_oracle(H, rows):
+    from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+
+    x, lab = mnist.synthetic_mnist(rows, seed=1, image_size=H[0], pixel_max=1)
+    nn = M.NeuralNetwork(H)
+    nn.W[0] *= 10
+    nn.W[1] *= 10
+    # make the oracle see exactly the bf16-rounded weights the tensor cores see
+    nn.W[0] = nn.W[0].bfloat16().double()
+    nn.b[0] = nn.b[0].bfloat16().double()
+    ref = nn.clone()
+    lr, reg = 0.5, 1e-3
+    g = M.backprop(ref, M.label_to_y(lab, 10), reg, M.feedforward(ref, x))
+    M.sgd_reference_step(ref, g, lr)
+
+    eng = MLPEngineBF16(H, rows, _info())
+    eng.load_params(nn)
+    xd = x.cuda()
+    eng.step(xd.data_ptr(), lab.cuda(), rows, lr, reg, rows, want_loss=True)
+    got = nn.clone()
+    eng.store_params(got)
+    # compare the UPDATE (lr * gradient), which is what the kernels computed
+    for name, w0, w_ref, w_got in (("W0", nn.W[0], ref.W[0], got.W[0]), ("b0", nn.b[0], ref.b[0], got.b[0]),
+                                   ("W1", nn.W[1], ref.W[1], got.W[1]), ("b1", nn.b[1], ref.b[1], got.b[1])):
+        du_ref, du_got = w_ref - w0, w_got - w0
+        err = (du_ref - du_got).abs().max() / du_ref.abs().max()
+        assert err < 3e-2, (name, float(err))
+    want_loss = -(M.label_to_y(lab, 10) * torch.log(M.feedforward(nn, x).yc)).sum().item()
+    assert abs(float(eng.loss.item()) - want_loss) < 2e-2 * want_loss
+    # the bf16 compute copy tracks the fp32 master
+    w1 = eng.params.tensor[: eng.n_w1]
+    assert torch.equal(eng.w1c.tensor.float(), w1.bfloat16().float())
+
+
+def test_bf16_training_learns():
+    from cme213_sp18_b200.parallel.dp_trainer import parallel_train
+
+    x, lab = mnist.synthetic_mnist(4000, seed=2, pixel_max=1)
+    nn = M.NeuralNetwork([784, 128, 10])
+    out = parallel_train(nn, x, lab, 0.5, 1e-4, 6, 400, info=_info(), print_every=5, log=lambda *_: None)
+    assert out["iterations"] == 60
+    acc = M.precision(M.predict(nn, x), lab)
+    assert acc > 0.95, acc
+    assert out["losses"][0][1] > out["losses"][-1][1]
+
+
+def test_bf16_predict_matches_cpu():
+    from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+
+    x, lab = mnist.synthetic_mnist(1000, seed=4, pixel_max=1)
+    nn = M.NeuralNetwork([784, 100, 10])
+    M.train(nn, x, lab, 0.5, 0.0, 3, 200)
+    eng = MLPEngineBF16(nn.H, 300, _info())
+    eng.load_params(nn)
+    got = eng.predict(x).cpu().long()
+    want = M.predict(nn, x)
+    assert (got == want).double().mean() > 0.99
+
+
+@pytest.mark.parametrize("hidden", [100, 37])
+def test_fp64_engine_grade_tolerance(hidden, tmp_path):
+    """Grade-mode contract: parallel (GPU fp64) vs serial within 1e-7 relative inf-norm
+    (ref fpcode/utils/tests.cpp:51-75, grade preset 3: lr 0.025, batch 800, 1 epoch)."""
+    from cme213_sp18_b200.parallel.dp_trainer import parallel_train
+
+    x, lab = mnist.synthetic_mnist(2400 + 123, seed=5)           # raw 0..255 pixels, short last batch
+    seq = M.NeuralNetwork([784, hidden, 10])
+    par = seq.clone()
+    M.train(seq, x, lab, 0.025, 1e-4, 1, 800)
+    parallel_train(par, x, lab, 0.025, 1e-4, 1, 800, info=_info(), precision="fp64")
+    rep = grading.check_nn_errors(seq, par, filename=tmp_path / "NNErrors.txt", log=lambda *_: None)
+    assert rep["passed"], rep
+
+
+def _torchrun(script: Path, nproc: int, port: int, timeout: int = 300):
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    return subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                           f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
+                           "--master-port", str(port), str(script)],
+                          capture_output=True, text=True, env=env, timeout=timeout)
+
+
+@pytest.mark.multigpu
+@pytest.mark.timeout(400)
+def test_two_gpu_fused_allreduce_matches_single_gpu_and_nccl(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(f"""
+import sys, torch
+sys.path.insert(0, {str(ROOT)!r})
+from cme213_sp18_b200.models import mlp as M
+from cme213_sp18_b200.parallel.dist import init_distributed, shutdown, DistInfo
+from cme213_sp18_b200.parallel.dp_trainer import parallel_train
+from cme213_sp18_b200.utils import mnist, grading
+info = init_distributed()
+x, lab = mnist.synthetic_mnist(3200, seed=0, pixel_max=1)
+base = M.NeuralNetwork([784, 128, 10])
+fused, nccl, fp64 = base.clone(), base.clone(), base.clone()
+parallel_train(fused, x if info.rank == 0 else None, lab if info.rank == 0 else None, 0.5, 1e-4, 2, 800,
+               info=info, comm="fused", data_mode="owner")
+parallel_train(nccl, x, lab, 0.5, 1e-4, 2, 800, info=info, comm="nccl", data_mode="sharded")
+parallel_train(fp64, x, lab, 0.5, 1e-4, 2, 800, info=info, precision="fp64", data_mode="sharded")
+if info.rank == 0:
+    ser = base.clone()
+    M.train(ser, x, lab, 0.5, 1e-4, 2, 800)
+    r1 = grading.check_nn_errors(ser, fp64, filename={str(tmp_path / 'e1.txt')!r}, log=lambda *_: None)
+    assert r1["passed"], r1
+    for a, b in zip(fused.W + fused.b, nccl.W + nccl.b):
+        d = (a - b).abs().max() / b.abs().max()
+        assert d < 2e-3, float(d)
+    for a, b in zip(fused.W + fused.b, ser.W + ser.b):
+        d = (a - b).abs().max() / b.abs().max()
+        assert d < 5e-2, float(d)
+    print("TWO_GPU_OK")
+shutdown()
+""")
+    res = _torchrun(script, 2, 29541)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "TWO_GPU_OK" in res.stdout
