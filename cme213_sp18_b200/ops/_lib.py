@@ -33,6 +33,7 @@ _DEV_SIGS = {
     "cme_heat_bc": [P, P, c_int, c_int, c_int, c_float, P],
     "cme_heat_slab_step": [P, P, P, P, c_int, c_int, c_int, c_float, c_float, c_float, c_int, c_int, P],
     "cme_sanitize_compact": [P, c_size_t, P, P, P, c_size_t, P],
+    "cme_sanitize_compact_noalloc": [P, c_size_t, P, P, P],
     "cme_byte_histogram": [P, c_size_t, c_size_t, c_size_t, P, P],
     "cme_strided_histograms": [P, c_size_t, c_int, P, P],
     "cme_vigenere_shift": [P, P, c_size_t, P, c_int, c_int, P],

@@ -9,6 +9,8 @@
 // compaction, the index-of-coincidence search evaluates many lags per launch.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int kCompactThreads = 256;
@@ -266,3 +268,73 @@ int cme_lag_match_counts(const uint8_t* text, size_t n, int lag0, int num_lags,
 }
 
 }  // extern "C"
+
+// =============================================================================
+// Sanitise without any allocation
+// =============================================================================
+// cme_sanitize_compact() needs a small scratch array (one 32-bit counter per
+// 2048 input bytes) and asks the caller to bring it.  Some callers have no way
+// to do that: a plug-in that is handed device pointers by its host program and
+// is not allowed to call the CUDA allocator itself, or a service that pins its
+// whole memory budget at start-up and treats any later cudaMalloc (which also
+// stalls every stream of the device while it runs) as a fault.  For them the
+// scratch below lives inside the library image: every GPU that loads
+// libcme213b.so carries these 128 KiB from load until the process exits.
+//
+// kNoAllocMaxBytes is the largest input the fixed array can serve.
+constexpr size_t kNoAllocMaxBytes = (size_t)64 << 20;                          // 64 MiB of text
+constexpr size_t kNoAllocSlots = kNoAllocMaxBytes / kCompactTile;             // 32768 counters
+static __device__ __align__(256) uint32_t g_noalloc_counts[kNoAllocSlots];    // 128 KiB per GPU
+
+namespace {
+
+// In host code `g_noalloc_counts` is only a handle for the runtime, never an
+// address a kernel may dereference: the device address has to be asked for, per
+// device, with that device current.
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_addr[64] = {nullptr};
+
+int noalloc_scratch_for_current_device(uint32_t** out) {
+    int dev = 0;
+    CME_CUDA(cudaGetDevice(&dev));
+    CME_CHECK_ARG(dev >= 0 && dev < 64, "cme_sanitize_compact_noalloc: device ordinal %d", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (g_noalloc_addr[dev] == nullptr) {
+        uint32_t* p = nullptr;
+        CME_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_counts));
+        g_noalloc_addr[dev] = p;
+    }
+    *out = g_noalloc_addr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int cme_sanitize_compact_noalloc(const uint8_t* in, size_t n, uint8_t* out,
+                                            int64_t* out_count, void* stream) {
+    CME_CHECK_ARG(out_count != nullptr, "cme_sanitize_compact_noalloc: out_count is null");
+    CME_CHECK_ARG(n <= kNoAllocMaxBytes,
+                  "cme_sanitize_compact_noalloc: %zu bytes exceed the built-in scratch limit of %zu "
+                  "bytes; use cme_sanitize_compact with caller scratch",
+                  n, kNoAllocMaxBytes);
+    cudaStream_t st = cme::as_stream(stream);
+    if (n == 0) {
+        CME_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int64_t), st));
+        return 0;
+    }
+    CME_CHECK_ARG(in && out, "cme_sanitize_compact_noalloc: null buffer");
+    uint32_t* counts = nullptr;
+    int rc = noalloc_scratch_for_current_device(&counts);
+    if (rc) return rc;
+    // Nothing in the shared array has to start at zero: the first kernel writes
+    // every counter this call reads (slots 0..nblocks-1) before the scan reads
+    // them, so whatever an earlier call left behind is overwritten.
+    const size_t nblocks = (n + kCompactTile - 1) / kCompactTile;
+    compact_count<<<(unsigned)nblocks, kCompactThreads, 0, st>>>(in, n, counts);
+    CME_LAUNCH_CHECK();
+    compact_scan<<<1, 1024, 0, st>>>(counts, (uint32_t)nblocks, out_count);
+    CME_LAUNCH_CHECK();
+    compact_scatter<<<(unsigned)nblocks, kCompactThreads, 0, st>>>(in, n, counts, out);
+    CME_LAUNCH_CHECK();
+    return 0;
+}

@@ -79,6 +79,26 @@ int cme_heat_slab_step(float* next, const float* curr, float* up_next_ghost,
  * +16 bytes of device memory. */
 int cme_sanitize_compact(const uint8_t* in, size_t n, uint8_t* out, int64_t* out_count,
                          void* scratch, size_t scratch_bytes, void* stream);
+/* The same operation for callers that cannot provide scratch memory: a plug-in
+ * that only receives device pointers from its host application and may not call
+ * the CUDA allocator, or a long-running service that fixes its memory budget at
+ * start-up and forbids later cudaMalloc/cudaFree (each of which also stalls the
+ * whole device while it runs).  The counters live in a 128 KiB array inside the
+ * library image, held by every GPU that loads the library until the process
+ * exits, which limits one call to n <= 64 MiB (67108864 bytes); a larger n is
+ * rejected with a negative return and a message naming the limit.  The call
+ * itself performs no cudaMalloc, cudaFree or other allocating call.
+ *   - The first call on each device looks up the array's device address (that
+ *     device must be current, as for every call).  Make that first call before
+ *     any stream capture is begun on the device.
+ *   - All calls on a device share the one array.  It keeps whatever the last call
+ *     left in it; this is harmless because a call overwrites every counter it
+ *     later reads.  Two calls that can run at the same time on one GPU (different
+ *     streams, or different threads) race on it: serialise them.
+ * Results are identical to cme_sanitize_compact.  This entry point has no
+ * counterpart in the reference. */
+int cme_sanitize_compact_noalloc(const uint8_t* in, size_t n, uint8_t* out, int64_t* out_count,
+                                 void* stream);
 /* counts[256] (device uint64, zeroed by the call) of text[offset + k*stride]. */
 int cme_byte_histogram(const uint8_t* text, size_t n, size_t stride, size_t offset,
                        unsigned long long* counts, void* stream);
