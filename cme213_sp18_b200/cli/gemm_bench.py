@@ -1,0 +1,97 @@
+"""GEMM benchmark (ref fpcode/utils/tests.cpp:126-280, `main -g 4`).
+
+fp64: this repo's cme_dgemm vs cuBLAS DGEMM (torch.matmul) on the reference's two shapes
+(800,1000,784) and (800,10,1000) with alpha=2, beta=5, 1 warm-up + 10 timed calls each, pass if the
+relative inf-norm of the difference is <= 1e-12.  bf16: the tcgen05 GEMM vs cuBLAS on large
+tile-aligned shapes (library call for comparison only)."""
+from __future__ import annotations
+
+import argparse
+
+import torch
+
+from ..ops import device as dev
+from ..utils.timing import time_cuda_ms
+
+NUM_ITERS = 10
+GEMM_TOL = 1e-12
+
+
+def create_mats(M, N, K):
+    """Deterministic fill in the spirit of createMATS (ref tests.cpp:77-99)."""
+    i = torch.arange(M, dtype=torch.float64).view(-1, 1)
+    A = ((i * K + torch.arange(K, dtype=torch.float64)) % 1000) / 1000.0
+    k = torch.arange(K, dtype=torch.float64).view(-1, 1)
+    B = ((k * N + torch.arange(N, dtype=torch.float64)) % 777) / 777.0
+    C = ((i * N + torch.arange(N, dtype=torch.float64)) % 333) / 333.0
+    return A, B, C
+
+
+def test_gemm_fp64(M, N, K, alpha=2.0, beta=5.0, log=print) -> bool:
+    A, B, C0 = create_mats(M, N, K)
+    colmajor = lambda t: t.T.contiguous().cuda()          # noqa: E731
+    dA, dB = colmajor(A), colmajor(B)
+    c_lib, c_own = colmajor(C0), colmajor(C0)
+    Ag, Bg = A.cuda(), B.cuda()
+    ref = C0.cuda().clone()
+
+    def lib_call():
+        ref.copy_(alpha * (Ag @ Bg) + beta * ref)
+
+    def own_call():
+        dev.dgemm(False, False, M, N, K, alpha, dA, M, dB, K, beta, c_own, M)
+
+    # beta accumulates over the 1 + NUM_ITERS calls on both sides, as in the reference
+    lib_call()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(NUM_ITERS):
+        lib_call()
+    e1.record()
+    torch.cuda.synchronize()
+    t_lib = e0.elapsed_time(e1) * 1e-3
+    own_call()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(NUM_ITERS):
+        own_call()
+    e1.record()
+    torch.cuda.synchronize()
+    t_own = e0.elapsed_time(e1) * 1e-3
+    got = c_own.T
+    rel = float(((got - ref).abs().sum(dim=1).max() / ref.abs().sum(dim=1).max()).item())
+    ok = rel <= GEMM_TOL
+    log(f"*** GEMM ({M},{N},{K}) ***")
+    log(f"Time for reference GEMM implementation: {t_lib:.6f} seconds")
+    log(f"Time for my GEMM implementation: {t_own:.6f} seconds")
+    log(f"Relative Inf error = {rel:.3e}  ->  {'PASSED' if ok else 'FAILED'}")
+    return ok
+
+
+def bench_bf16(M, N, K, log=print) -> dict:
+    a = torch.randn((M, K), device="cuda").bfloat16()
+    b = torch.randn((N, K), device="cuda").bfloat16()
+    out = torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+    ms_own = time_cuda_ms(lambda: dev.gemm_bf16(a, b, out), warmup=3, iters=10)
+    ms_lib = time_cuda_ms(lambda: torch.matmul(a, b.T), warmup=3, iters=10)
+    err = float(((out.float() - (a.float() @ b.float().T)).abs().max()).item())
+    tf = lambda ms: 2.0 * M * N * K / ms / 1e9            # noqa: E731
+    log(f"bf16 ({M},{N},{K}): tcgen05 {ms_own:.3f} ms = {tf(ms_own):.0f} TFLOP/s | cuBLAS {ms_lib:.3f} ms = "
+        f"{tf(ms_lib):.0f} TFLOP/s | max abs err {err:.3g}")
+    return {"ms_own": ms_own, "ms_cublas": ms_lib, "tflops_own": tf(ms_own), "tflops_cublas": tf(ms_lib)}
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="gemm_bench", description=__doc__)
+    ap.add_argument("--no-bf16", action="store_true")
+    args = ap.parse_args(argv)
+    ok = test_gemm_fp64(800, 1000, 784) & test_gemm_fp64(800, 10, 1000)
+    if not args.no_bf16:
+        for shape in ((8192, 8192, 8192), (65536, 8192, 832), (4096, 4096, 4096)):
+            bench_bf16(*shape)
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

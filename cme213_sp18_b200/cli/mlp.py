@@ -1,0 +1,131 @@
+"""fpcode driver with the reference's flags (ref fpcode/main.cpp:34-276).
+
+    python -m cme213_sp18_b200.cli.mlp -g 2                  # one GPU
+    python -m torch.distributed.run --nproc-per-node 4 -m cme213_sp18_b200.cli.mlp -g 2
+
+  -n hidden units (1000)   -r L2 reg (1e-4)    -l learning rate (0.001)   -e epochs (20)
+  -b batch size (800)      -g grade mode (0)   -p print_every (0)         -s also run serial
+  -d debug (weight dumps + CpuGpuDiff.txt)
+Grade presets 1-3 fix the hyper-parameters and turn on serial + debug; 4 runs the GEMM benchmark
+(ref main.cpp:113-161).  Additions: --precision {auto,bf16,fp64} (auto = fp64 in grade/debug mode,
+bf16 otherwise), --comm {fused,nccl}, --data-dir, --train-size, --pixel-max, --outdir.
+"""
+from __future__ import annotations
+
+import argparse
+import time
+from pathlib import Path
+
+import torch
+
+from ..models import mlp as M
+from ..parallel.dist import init_distributed, shutdown
+from ..parallel.dp_trainer import parallel_train
+from ..utils import grading, mnist
+
+PRESETS = {1: dict(reg=1e-4, lr=0.001, epochs=40, batch=800, neurons=100, print_every=0),
+           2: dict(reg=1e-4, lr=0.01, epochs=10, batch=800, neurons=100, print_every=0),
+           3: dict(reg=1e-4, lr=0.025, epochs=1, batch=800, neurons=100, print_every=1)}
+
+
+def build_parser() -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(prog="mlp", description=__doc__,
+                                 formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("-n", dest="neurons", type=int, default=1000)
+    ap.add_argument("-r", dest="reg", type=float, default=1e-4)
+    ap.add_argument("-l", dest="lr", type=float, default=0.001)
+    ap.add_argument("-e", dest="epochs", type=int, default=20)
+    ap.add_argument("-b", dest="batch", type=int, default=800)
+    ap.add_argument("-g", dest="grade", type=int, default=0)
+    ap.add_argument("-p", dest="print_every", type=int, default=0)
+    ap.add_argument("-s", dest="run_seq", action="store_true")
+    ap.add_argument("-d", dest="debug", action="store_true")
+    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp64"])
+    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--data-dir", default="data")
+    ap.add_argument("--train-size", type=int, default=mnist.NUM_TRAIN)
+    ap.add_argument("--test-size", type=int, default=mnist.NUM_TEST)
+    ap.add_argument("--pixel-max", type=int, default=255)
+    ap.add_argument("--outdir", default="Outputs")
+    ap.add_argument("--device", default=None, help="cpu forces the gloo/CPU schedule")
+    return ap
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
+    info = init_distributed(args.device)
+    rank0 = info.is_main
+    ndev = torch.cuda.device_count() if info.device.type == "cuda" else 0
+    if rank0:
+        print(f"Number of processes = {info.world}")
+        print(f"Number of CUDA devices = {ndev}")
+    if args.grade in PRESETS:
+        for k, v in PRESETS[args.grade].items():
+            setattr(args, k, v)
+        args.run_seq = args.debug = True
+    if args.grade == 4:
+        if rank0:
+            from .gemm_bench import main as gemm_main
+
+            gemm_main([])
+        shutdown()
+        return 0
+    H = [mnist.IMAGE_SIZE, args.neurons, mnist.NUM_CLASSES]
+    nn = M.NeuralNetwork(H)
+    seq_nn = M.NeuralNetwork(H)
+    out = Path(args.outdir)
+    x_train = l_train = x_dev = l_dev = x_test = None
+    if rank0:
+        print(f"num_neuron={args.neurons}, reg={args.reg}, learning_rate={args.lr}, "
+              f"num_epochs={args.epochs}, batch_size={args.batch}")
+        print("Loading training data...")
+        x, lab, x_test, source = mnist.load_or_synthesize(args.data_dir, args.train_size, args.test_size,
+                                                          pixel_max=args.pixel_max)
+        print(f"Training data stats... ({source})")
+        print(f"Size of x_train, N =  {x.shape[0]}")
+        print(f"Size of label_train = {lab.shape[0]}")
+        (x_train, l_train), (x_dev, l_dev) = M.split_train_dev(x, lab)
+    if rank0 and args.run_seq:
+        print("Start Sequential Training")
+        t0 = time.perf_counter()
+        M.train(seq_nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
+                args.print_every, args.debug, outdir=str(out / "CPUmats"))
+        print(f"Time for Sequential Training: {time.perf_counter() - t0} seconds")
+        prec = M.precision(M.predict(seq_nn, x_dev), l_dev)
+        print(f"Precision on validation set for sequential training = {prec}")
+    if rank0:
+        print("\nStart Parallel Training")
+    precision = args.precision
+    if precision == "auto":
+        precision = "fp64" if (args.grade or args.debug) else "bf16"
+    dl = grading.CpuGpuDiffLog(out / "CpuGpuDiff.txt", out / "CPUmats") if (args.debug and rank0) else None
+    t0 = time.perf_counter()
+    if info.device.type == "cpu" and info.world > 1:
+        # the gloo schedule wants the data on every rank
+        import torch.distributed as dist
+
+        box = [x_train, l_train]
+        dist.broadcast_object_list(box, src=0)
+        x_train, l_train = box
+    parallel_train(nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
+                   args.print_every, args.debug, info=info, precision=precision, comm=args.comm,
+                   debug_log=dl)
+    if rank0:
+        print(f"Time for Parallel Training: {time.perf_counter() - t0} seconds")
+        prec = M.precision(M.predict(nn, x_dev), l_dev)
+        print(f"Precision on validation set for parallel training = {prec}")
+        grading.save_label(out / "Pred_testset.txt", M.predict(nn, x_test))
+    rc = 0
+    if (args.grade or args.debug) and rank0:
+        if dl:
+            dl.close()
+        print("\nGrading mode on. Checking for correctness")
+        rep = grading.check_nn_errors(seq_nn, nn, out / "NNErrors.txt",
+                                      rel_tol=1e-7 if precision == "fp64" else 5e-2)
+        rc = 0 if (rep["passed"] or not args.run_seq) else 3
+    shutdown()
+    return rc
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

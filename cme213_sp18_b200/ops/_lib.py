@@ -150,6 +150,8 @@ def ptr(t: torch.Tensor | None) -> int | None:
     """Device (or host) address of a tensor; None passes NULL."""
     if t is None:
         return None
+    if isinstance(t, int):          # a raw (possibly offset or peer-mapped) address
+        return t
     return int(t.data_ptr())
 
 

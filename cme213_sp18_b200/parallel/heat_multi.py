@@ -1,0 +1,88 @@
+"""Multi-GPU 2-D heat diffusion: row-slab decomposition with the halo exchange fused into the
+sweep kernel.
+
+The reference's hw3 is single-GPU (ref hw3code/gpuStencil.cu); BASELINE.json asks for the
+32768^2 order-8 grid across 8 GPUs.  Each rank owns `rows_local` interior rows plus `border`
+ghost rows above and below.  One launch per step computes the slab, applies the border decay on
+the physical borders it touches, and stores its first / last `border` rows straight into the
+neighbours' ghost rows through peer-mapped pointers (no separate exchange, no host staging).  A
+flag barrier over peer memory orders the steps.  The oracle is the single-device math.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..ops import device as dev
+from ..utils.heat import SimParams
+from .dist import DistInfo, SymmetricTensor
+
+
+class HeatSlabs:
+    def __init__(self, p: SimParams, info: DistInfo):
+        if p.ny % info.world != 0:
+            raise ValueError(f"ny={p.ny} must be divisible by the number of ranks ({info.world})")
+        self.p, self.info = p, info
+        self.b = p.border
+        self.rows = p.ny // info.world
+        if self.rows < self.b:
+            raise ValueError("slab thinner than the stencil border")
+        self.gx = p.gx
+        self.ly = self.rows + 2 * self.b                   # local grid rows incl. ghosts
+        n = self.ly * self.gx
+        self.buf = [SymmetricTensor(n, torch.float32, info), SymmetricTensor(n, torch.float32, info)]
+        self.pads = SymmetricTensor(1024, torch.int32, info)
+        self.pads_dev = self.pads.ptr_table_dev()
+        self.cur = 0
+        self.s = float(np.float32(p.bc_scale))
+
+    def grid(self, which: int) -> torch.Tensor:
+        return self.buf[which].tensor.view(self.ly, self.gx)
+
+    def load(self, grid0: torch.Tensor | np.ndarray) -> None:
+        """Every rank takes its slab (with ghost rows) out of the full initial grid."""
+        g = torch.as_tensor(grid0)
+        r0 = self.info.rank * self.rows
+        sl = g[r0: r0 + self.ly].to(self.info.device, torch.float32)
+        self.grid(0).copy_(sl)
+        self.grid(1).copy_(sl)
+        self.cur = 0
+        torch.cuda.synchronize()
+        if self.info.world > 1:
+            dist.barrier()
+
+    def step(self) -> None:
+        info, b, gx = self.info, self.b, self.gx
+        cur, nxt = self.cur, self.cur ^ 1
+        up = down = None
+        if info.rank > 0:                                  # neighbour above: its bottom ghost rows
+            up = self.buf[nxt].peer_ptrs[info.rank - 1] + (self.rows + b) * gx * 4
+        if info.rank < info.world - 1:                     # neighbour below: its top ghost rows
+            down = self.buf[nxt].peer_ptrs[info.rank + 1]
+        dev.heat_slab_step(self.grid(nxt), self.grid(cur), up, down, self.rows, self.p.order,
+                           self.p.xcfl, self.p.ycfl, self.s, info.rank == 0,
+                           info.rank == info.world - 1)
+        if info.world > 1:
+            dev.peer_barrier(self.pads_dev, info.rank, info.world, 2, 0)
+        self.cur = nxt
+
+    def run(self, iters: int | None = None) -> None:
+        for _ in range(self.p.iters if iters is None else iters):
+            self.step()
+
+    def gather(self) -> torch.Tensor:
+        """Full (gy x gx) grid on every rank: the owned interior rows of every slab plus the
+        physical top border of rank 0 and bottom border of the last rank."""
+        info, b = self.info, self.b
+        g = self.grid(self.cur)
+        mine = g[b: b + self.rows].contiguous()
+        if info.world == 1:
+            return g.clone()
+        parts = [torch.empty_like(mine) for _ in range(info.world)]
+        dist.all_gather(parts, mine)
+        top = g[:b].contiguous()
+        bottom = g[self.ly - b:].contiguous()
+        dist.broadcast(top, src=0)
+        dist.broadcast(bottom, src=info.world - 1)
+        return torch.cat([top] + parts + [bottom], dim=0)

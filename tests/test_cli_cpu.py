@@ -1,0 +1,61 @@
+"""Command-line drivers that run without a GPU."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def run_module(mod, *args, cwd=None, timeout=300):
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="4")
+    return subprocess.run([sys.executable, "-m", mod, *map(str, args)], capture_output=True, text=True,
+                          cwd=cwd, env=env, timeout=timeout)
+
+
+def test_mlp_cli_grade3_on_cpu(tmp_path):
+    """Grade preset 3 end to end on the CPU schedule: serial + parallel + checkNNErrors."""
+    res = run_module("cme213_sp18_b200.cli.mlp", "-g", "3", "--device", "cpu", "--train-size", "2000",
+                     "--test-size", "50", "--data-dir", tmp_path / "none", "--outdir", tmp_path / "Outputs",
+                     cwd=tmp_path)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "num_neuron=100, reg=0.0001, learning_rate=0.025, num_epochs=1, batch_size=800" in res.stdout
+    assert "Precision on validation set for parallel training" in res.stdout
+    assert "Correctness test failed" not in res.stdout
+    out = tmp_path / "Outputs"
+    assert (out / "NNErrors.txt").exists() and (out / "CpuGpuDiff.txt").exists()
+    assert (out / "CPUmats" / "SequentialW0-0.mat").exists()
+    assert len((out / "Pred_testset.txt").read_text()) == 50
+
+
+def test_mlp_cli_flags_parse():
+    from cme213_sp18_b200.cli.mlp import PRESETS, build_parser
+
+    a = build_parser().parse_args("-n 64 -r 0.5 -l 0.1 -e 3 -b 16 -g 0 -p 2 -s -d".split())
+    assert (a.neurons, a.reg, a.lr, a.epochs, a.batch, a.print_every, a.run_seq, a.debug) == \
+        (64, 0.5, 0.1, 3, 16, 2, True, True)
+    d = build_parser().parse_args([])
+    assert (d.neurons, d.reg, d.lr, d.epochs, d.batch) == (1000, 1e-4, 0.001, 20, 800)   # ref main.cpp:58-67
+    assert PRESETS[1]["epochs"] == 40 and PRESETS[2]["lr"] == 0.01 and PRESETS[3]["print_every"] == 1
+
+
+def test_radix_and_parity_cli():
+    r = run_module("cme213_sp18_b200.cli.radix", "--size", "200000")
+    assert r.returncode == 0 and "Test5: PASSED" in r.stdout and "all sorts correct" in r.stdout
+    p = run_module("cme213_sp18_b200.cli.parity", "--size", "1000000")
+    assert p.returncode == 0 and p.stdout.count("Sum Even") == 2
+
+
+def test_sim_params_file_roundtrip(tmp_path):
+    from cme213_sp18_b200.utils.heat import SimParams
+
+    f = tmp_path / "params.in"
+    f.write_text("4096 4096\n1 1 \n400\n8\n")                 # the reference's params.in verbatim
+    p = SimParams.from_file(f)
+    assert (p.nx, p.ny, p.lx, p.ly, p.iters, p.order) == (4096, 4096, 1.0, 1.0, 400, 8)
+    p.to_file(tmp_path / "p2.in")
+    assert SimParams.from_file(tmp_path / "p2.in") == p
+    with pytest.raises(ValueError):
+        SimParams(order=3)
