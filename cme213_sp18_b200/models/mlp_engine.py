@@ -27,8 +27,11 @@ class MLPEngineBF16:
     than one rank all three live in symmetric memory: the fused all-reduce + SGD kernel reads
     every rank's gradients and writes every rank's weights through peer pointers."""
 
-    def __init__(self, H, max_rows: int, info: DistInfo | None = None, comm: str = "fused"):
+    def __init__(self, H, max_rows: int, info: DistInfo | None = None, comm: str = "fused",
+                 tail: str = "tc"):
+        """tail: "tc" runs layer 2 / dW2 on the tensor cores, "simt" on the CUDA-core kernels."""
         self.info = info or DistInfo(device=torch.device("cuda", torch.cuda.current_device()))
+        self.tail = tail
         self.D, self.Hh, self.C = H
         if self.C != 10:
             raise ValueError("the bf16 engine is built for 10 classes")
@@ -53,6 +56,8 @@ class MLPEngineBF16:
         self.a1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
         self.dz1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
         self.dz2 = torch.zeros((max_rows, 16), dtype=torch.float32, device=d)
+        self.dz2b = torch.zeros((max_rows, 64), dtype=torch.bfloat16, device=d)   # bf16 copy for dW2
+        self.w2c = torch.zeros((16, self.ldh), dtype=torch.bfloat16, device=d)    # bf16 W2, rows >= C zero
         self.pred = torch.zeros(max_rows, dtype=torch.int32, device=d)
         self.loss = torch.zeros(1, dtype=torch.float32, device=d)
         self.use_mc = False
@@ -75,6 +80,7 @@ class MLPEngineBF16:
         w2.copy_(nn.W[1].to(w2.device, torch.float32))
         b2.copy_(nn.b[1].to(b2.device, torch.float32))
         self.w1c.tensor.copy_(self.params.tensor[: self.n_w1].to(torch.bfloat16))
+        self._recast_w2()
         torch.cuda.synchronize()
         if self.info.world > 1:
             dist.barrier()
@@ -87,6 +93,10 @@ class MLPEngineBF16:
         nn.W[1] = w2.double().cpu().contiguous()
         nn.b[1] = b2.double().cpu().contiguous()
 
+    def _recast_w2(self) -> None:
+        _, w2, _ = self._views(self.params.tensor)
+        dev.f32_to_bf16_2d(w2, self.Hh, self.w2c, self.ldh, self.C, self.Hh)
+
     # ---- one minibatch slice ----
     def stage(self, x_u8_ptr: int, rows: int) -> None:
         """uint8 pixels at x_u8_ptr (local or peer-mapped) -> bf16 rows + ones column."""
@@ -97,14 +107,23 @@ class MLPEngineBF16:
         _, w2, b2 = self._views(self.params.tensor)
         _, _, gb2 = self._views(self.grads.tensor)
         dev.mlp_fwd1(self.xb, self.w1c.tensor, self.a1, rows, self.K, self.Hh)
-        dev.mlp_fwd2_softmax(self.a1, w2, b2, labels, self.dz2 if want_grad else None,
-                             self.loss if want_loss else None, self.pred,
-                             gb2 if want_grad else None, scale, rows, self.Hh, self.C)
+        if self.tail == "tc":
+            dev.mlp_fwd2_tc(self.a1, self.w2c, b2, labels, self.dz2 if want_grad else None,
+                            self.dz2b if want_grad else None, self.loss if want_loss else None,
+                            self.pred, gb2 if want_grad else None, scale, rows, self.Hh, self.C)
+        else:
+            dev.mlp_fwd2_softmax(self.a1, w2, b2, labels, self.dz2 if want_grad else None,
+                                 self.loss if want_loss else None, self.pred,
+                                 gb2 if want_grad else None, scale, rows, self.Hh, self.C)
 
     def backward(self, rows: int) -> None:
         _, w2, _ = self._views(self.params.tensor)
         gw1, gw2, _ = self._views(self.grads.tensor)
-        dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, gw2, rows, self.Hh, self.C)
+        if self.tail == "tc":
+            dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, None, rows, self.Hh, self.C)
+            dev.mlp_dw2_tc(self.a1, self.dz2b, gw2, rows, self.Hh, self.C)
+        else:
+            dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, gw2, rows, self.Hh, self.C)
         dev.mlp_dw1(self.dz1, self.xb, gw1, rows, self.K, self.Hh, self.ldx)
 
     def update(self, lr: float, reg: float) -> None:
@@ -117,6 +136,8 @@ class MLPEngineBF16:
             dev.allreduce_sgd([self.grads.tensor.data_ptr()], [self.params.tensor.data_ptr()],
                               [self.w1c.tensor.data_ptr()], 0, self.n_total, self.n_w1, self.ldx,
                               self.D, w2_begin, w2_end, lr, reg)
+            if self.tail == "tc":
+                self._recast_w2()
             return
         if info.world > 1:
             dev.peer_barrier(self.pads_dev, info.rank, info.world, 0, 0)   # all gradients complete
@@ -131,6 +152,8 @@ class MLPEngineBF16:
                               lr, reg)
         if info.world > 1:
             dev.peer_barrier(self.pads_dev, info.rank, info.world, 1, 0)   # all weights visible
+        if self.tail == "tc":
+            self._recast_w2()
 
     def step(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
              norm: float, want_loss: bool = False) -> None:

@@ -52,6 +52,9 @@ _DEV_SIGS = {
     "cme_mlp_fwd1": [P, P, P, P, c_i64, c_int, c_int, c_int, c_int, P],
     "cme_mlp_fwd2_softmax": [P, P, P, P, P, P, P, P, c_float, c_i64, c_int, c_int, c_int, P],
     "cme_mlp_bwd_elem": [P, P, P, P, P, c_i64, c_int, c_int, c_int, P],
+    "cme_mlp_fwd2_tc": [P, P, P, P, P, P, P, P, P, c_float, c_i64, c_int, c_int, c_int, P],
+    "cme_mlp_dw2_tc": [P, P, P, c_i64, c_int, c_int, c_int, P],
+    "cme_f32_to_bf16_2d": [P, c_int, P, c_int, c_int, c_int, P],
     "cme_mlp_dw1": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P],
     "cme_gemm_bf16": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P],
     "cme_allreduce_sgd": [P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, P],

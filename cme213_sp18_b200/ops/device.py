@@ -277,6 +277,27 @@ def mlp_bwd_elem(A1, dz2, W2, dZ1, gW2, rows: int, H: int, C: int = 10) -> None:
     _count()
 
 
+def mlp_fwd2_tc(A1, W2c, b2, labels, dz2, dz2b, loss_sum, pred, gb2, scale: float, rows: int, H: int,
+                C: int = 10) -> None:
+    """Layer 2 + softmax + CE gradient on tcgen05 with everything after the GEMM in the epilogue."""
+    check(device_lib().cme_mlp_fwd2_tc(ptr(A1), ptr(W2c), ptr(b2), ptr(labels), ptr(dz2), ptr(dz2b),
+                                       ptr(loss_sum), ptr(pred), ptr(gb2), scale, rows, H,
+                                       A1.shape[1], C, stream_ptr()), "cme_mlp_fwd2_tc")
+    _count()
+
+
+def mlp_dw2_tc(A1, dz2b, gW2, rows: int, H: int, C: int = 10) -> None:
+    check(device_lib().cme_mlp_dw2_tc(ptr(A1), ptr(dz2b), ptr(gW2), rows, H, A1.shape[1], C,
+                                      stream_ptr()), "cme_mlp_dw2_tc")
+    _count()
+
+
+def f32_to_bf16_2d(src, ld_src: int, dst, ld_dst: int, rows: int, cols: int) -> None:
+    check(device_lib().cme_f32_to_bf16_2d(ptr(src), ld_src, ptr(dst), ld_dst, rows, cols,
+                                          stream_ptr()), "cme_f32_to_bf16_2d")
+    _count()
+
+
 def mlp_dw1(dZ1, X, gW1, rows: int, K: int, H: int, ldg: int) -> None:
     check(device_lib().cme_mlp_dw1(ptr(dZ1), ptr(X), ptr(gW1), rows, K, H, X.shape[1], dZ1.shape[1],
                                    ldg, stream_ptr()), "cme_mlp_dw1")

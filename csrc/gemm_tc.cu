@@ -84,14 +84,29 @@ __device__ __forceinline__ void teardown(Barriers* bars, uint32_t tmem_cols, int
     }
 }
 
+// Arguments of the layer-2 epilogue (EPI == 2): the 16 accumulator columns of a
+// row are its 10 logits; the epilogue finishes the forward pass in registers.
+struct SoftmaxEpi {
+    const float* b2;
+    const int32_t* labels;
+    float* dz2;              // [rows][16] fp32, may be null
+    __nv_bfloat16* dz2b;     // [rows][64] bf16 copy for the tensor-core dW2 product, may be null
+    float* loss_sum;         // may be null
+    int32_t* pred;           // may be null
+    float* gb2;              // may be null
+    float scale;
+    long long rows;
+    int classes;
+};
+
 // =============================================================================
 // K-major GEMM with fused epilogue and TMA store
 // =============================================================================
-template <int EPI /* 0 = identity, 1 = sigmoid */>
+template <int EPI /* 0 = identity, 1 = sigmoid, 2 = bias + softmax + cross-entropy gradient */>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                    const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K, int BN,
-                   uint32_t tmem_cols) {
+                   uint32_t tmem_cols, SoftmaxEpi sm) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
@@ -103,7 +118,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA);
         prefetch_tmap(&tmB);
-        prefetch_tmap(&tmC);
+        if (EPI != 2) prefetch_tmap(&tmC);
     }
     setup(bars, tmem_cols, warp, lane);
     const uint32_t tmem_base = bars->tmem_base;
@@ -173,6 +188,72 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            if constexpr (EPI == 2) {
+                uint32_t v[16];
+                tmem_ld_32x16(t_row, v);
+                tmem_ld_wait();
+                // logits are in registers: give the accumulator back before the math
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                const long long grow = (long long)m0 + row;
+                const bool valid = grow < sm.rows;
+                const int C = sm.classes;
+                float z[16];
+                float mx = -3.0e38f;
+                int arg = 0;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    z[c] = (c < C) ? __uint_as_float(v[c]) + __ldg(sm.b2 + c) : -3.0e38f;
+                    if (z[c] > mx) { mx = z[c]; arg = c; }
+                }
+                float ssum = 0.f;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    z[c] = (c < C) ? __expf(z[c] - mx) : 0.f;
+                    ssum += z[c];
+                }
+                const float inv = 1.f / ssum;
+                const int lab = (valid && sm.labels) ? sm.labels[grow] : -1;
+                float my_loss = 0.f;
+                float out[16];
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    const float p = z[c] * inv;
+                    out[c] = (valid && c < C) ? (p - (c == lab ? 1.f : 0.f)) * sm.scale : 0.f;
+                    if (c == lab) my_loss = -__logf(fmaxf(p, 1e-30f));
+                }
+                if (valid) {
+                    if (sm.dz2) {
+                        float4* d = reinterpret_cast<float4*>(sm.dz2 + grow * 16);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            d[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+                    }
+                    if (sm.dz2b) {
+                        uint4* d = reinterpret_cast<uint4*>(sm.dz2b + grow * 64);
+                        d[0] = make_uint4(pack_bf16(out[0], out[1]), pack_bf16(out[2], out[3]),
+                                          pack_bf16(out[4], out[5]), pack_bf16(out[6], out[7]));
+                        d[1] = make_uint4(pack_bf16(out[8], out[9]), pack_bf16(out[10], out[11]),
+                                          pack_bf16(out[12], out[13]), pack_bf16(out[14], out[15]));
+                    }
+                    if (sm.pred) sm.pred[grow] = arg;
+                }
+                if (sm.gb2) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        const float t = cme::warp_sum(out[c]);
+                        if (lane == 0 && c < C && t != 0.f) atomicAdd(sm.gb2 + c, t);
+                    }
+                }
+                if (sm.loss_sum) {
+                    const float t = cme::warp_sum(my_loss);
+                    if (lane == 0 && t != 0.f) atomicAdd(sm.loss_sum, t);
+                }
+                continue;
+            }
             for (int c = 0; c < BN / 64; ++c) {
                 // the staging buffer we are about to fill was handed to a TMA store
                 // two chunks ago: wait until that store has finished reading it
@@ -214,7 +295,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
-        if (leader) tma_store_wait_all<0>();
+        if (EPI != 2 && leader) tma_store_wait_all<0>();
     }
     teardown(bars, tmem_cols, warp);
 }
@@ -225,7 +306,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     float* __restrict__ G, int ldg, int M, int N, int m_tiles, int n_tiles,
-                    int kb_total, int BN, uint32_t tmem_cols) {
+                    int kb_total, int BN, uint32_t tmem_cols, int out_transposed) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
@@ -327,7 +408,14 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 uint32_t v[16];
                 tmem_ld_32x16(t_row + (uint32_t)(c * 16), v);
                 tmem_ld_wait();
-                if (h < M) {
+                if (h < M && out_transposed) {
+                    // G[d][h]: consecutive lanes hit consecutive addresses
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const int d = n0 + c * 16 + e;
+                        if (d < N) atomicAdd(G + (size_t)d * ldg + h, __uint_as_float(v[e]));
+                    }
+                } else if (h < M) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         const int d = n0 + c * 16 + g * 4;
@@ -443,14 +531,15 @@ int launch_kmajor(int epi, const void* A, const void* B, void* Cout, int64_t M, 
     const uint32_t cols = pow2_cols(2 * BN);
     const long long tiles = (long long)m_tiles * n_tiles;
     const int grid = (int)std::min<long long>(tiles, cme::sm_count());
+    SoftmaxEpi none{};
     if (epi == 1) {
         if ((rc = opt_in_smem(gemm_kmajor_kernel<1>, kSmemKMajor))) return rc;
         gemm_kmajor_kernel<1><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
-                                                                  BN, cols);
+                                                                  BN, cols, none);
     } else {
         if ((rc = opt_in_smem(gemm_kmajor_kernel<0>, kSmemKMajor))) return rc;
         gemm_kmajor_kernel<0><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
-                                                                  BN, cols);
+                                                                  BN, cols, none);
     }
     CME_LAUNCH_CHECK();
     return 0;
@@ -495,7 +584,54 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
     const long long units = (long long)m_tiles * n_tiles * kb_total;
     const int grid = (int)std::min<long long>(units, cme::sm_count());
     gemm_mnmajor_kernel<<<grid, kThreads, kSmemMNMajor, cme::as_stream(stream)>>>(
-        tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u);
+        tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u, 0);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int32_t* labels,
+                    float* dz2, void* dz2b, float* loss_sum, int32_t* pred, float* gb2, float scale,
+                    int64_t rows, int H, int ldh, int C, void* stream) {
+    CME_CHECK_ARG(A1 && W2c && b2 && rows > 0 && H > 0, "cme_mlp_fwd2_tc: bad argument");
+    CME_CHECK_ARG(C >= 1 && C <= 16, "cme_mlp_fwd2_tc: 1..16 classes (got %d)", C);
+    CME_CHECK_ARG(ldh % 8 == 0 && ldh >= H, "cme_mlp_fwd2_tc: ldh (%d)", ldh);
+    CME_CHECK_ARG((!dz2 && !dz2b) || labels, "cme_mlp_fwd2_tc: gradients need labels");
+    CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_fwd2_tc: too many rows");
+    const int m_tiles = (int)((rows + BM - 1) / BM);
+    CUtensorMap tmA, tmB;
+    int rc;
+    // the K extent is the true H: pad columns of A1 hold sigmoid(0) and must read as zero
+    if ((rc = make_map(&tmA, A1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, BK, BM))) return rc;
+    if ((rc = make_map(&tmB, W2c, (uint64_t)H, 16, (uint64_t)ldh, BK, 16))) return rc;
+    if ((rc = opt_in_smem(gemm_kmajor_kernel<2>, kSmemKMajor))) return rc;
+    SoftmaxEpi sm{b2, labels, dz2, (__nv_bfloat16*)dz2b, loss_sum, pred, gb2, scale, (long long)rows, C};
+    const int grid = std::min(m_tiles, cme::sm_count());
+    gemm_kmajor_kernel<2><<<grid, kThreads, kSmemKMajor, cme::as_stream(stream)>>>(
+        tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_dw2_tc(const void* A1, const void* dz2b, float* gW2, int64_t rows, int H, int ldh, int C,
+                   void* stream) {
+    CME_CHECK_ARG(A1 && dz2b && gW2 && rows > 0 && H > 0, "cme_mlp_dw2_tc: bad argument");
+    CME_CHECK_ARG(C >= 1 && C <= 16, "cme_mlp_dw2_tc: 1..16 classes (got %d)", C);
+    CME_CHECK_ARG(ldh % 8 == 0 && ldh >= H, "cme_mlp_dw2_tc: ldh (%d)", ldh);
+    CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_dw2_tc: too many rows");
+    const int m_tiles = (H + BM - 1) / BM;
+    const int kb_total = (int)((rows + BK - 1) / BK);
+    CUtensorMap tmA, tmB;
+    int rc;
+    if ((rc = make_map(&tmA, A1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BK))) return rc;
+    // dz2b rows are 64 bf16 wide of which 16 carry data: bound the map at 16 so the rest is
+    // zero-filled on chip and never read from memory
+    if ((rc = make_map(&tmB, dz2b, 16, (uint64_t)rows, 64, 64, BK))) return rc;
+    if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
+    const long long units = (long long)m_tiles * kb_total;
+    const int grid = (int)std::min<long long>(units, cme::sm_count());
+    // result tile is [h][c]; store it transposed into gW2[c][h]
+    gemm_mnmajor_kernel<<<grid, kThreads, kSmemMNMajor, cme::as_stream(stream)>>>(
+        tmA, tmB, gW2, H, H, C, m_tiles, 1, kb_total, 16, 512u, 1);
     CME_LAUNCH_CHECK();
     return 0;
 }

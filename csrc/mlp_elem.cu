@@ -183,7 +183,7 @@ fwd2_softmax_kernel(const __nv_bfloat16* __restrict__ A1, const float* __restric
 // ---- backward elementwise + dW2 ------------------------------------------------------
 // Thread owns 4 hidden columns and walks a chunk of rows; W2 for its columns and
 // the gW2 partial sums live in registers, dz2 rows are broadcast loads.
-template <int C>
+template <int C, bool WITH_GW2>
 __global__ void __launch_bounds__(256)
 bwd_elem_kernel(const __nv_bfloat16* __restrict__ A1, const float* __restrict__ dz2,
                 const float* __restrict__ W2, __nv_bfloat16* __restrict__ dZ1,
@@ -217,17 +217,31 @@ bwd_elem_kernel(const __nv_bfloat16* __restrict__ A1, const float* __restrict__ 
 #pragma unroll
             for (int c = 0; c < C; ++c) {
                 g = fmaf(d[c], w[c][e], g);
-                g2[c][e] = fmaf(d[c], a[e], g2[c][e]);
+                if (WITH_GW2) g2[c][e] = fmaf(d[c], a[e], g2[c][e]);
             }
             dz[e] = g * a[e] * (1.f - a[e]);
         }
         *reinterpret_cast<uint2*>(dZ1 + r * ldh + h) = make_uint2(pack2(dz[0], dz[1]), pack2(dz[2], dz[3]));
     }
+    if (WITH_GW2) {
 #pragma unroll
-    for (int c = 0; c < C; ++c)
+        for (int c = 0; c < C; ++c)
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-            if (h + e < H) atomicAdd(&gW2[(size_t)c * H + h + e], g2[c][e]);
+            for (int e = 0; e < 4; ++e)
+                if (h + e < H) atomicAdd(&gW2[(size_t)c * H + h + e], g2[c][e]);
+    }
+}
+
+// fp32 [rows][ld_src] -> bf16 [rows][ld_dst] (first `cols` columns; the rest untouched)
+__global__ void __launch_bounds__(256)
+f32_to_bf16_2d_kernel(const float* __restrict__ src, int ld_src, __nv_bfloat16* __restrict__ dst,
+                      int ld_dst, int rows, int cols) {
+    const int64_t total = (int64_t)rows * cols;
+    const int64_t gstride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gstride) {
+        const int r = (int)(i / cols), c = (int)(i % cols);
+        dst[(size_t)r * ld_dst + c] = __float2bfloat16_rn(src[(size_t)r * ld_src + c]);
+    }
 }
 
 }  // namespace
@@ -267,8 +281,7 @@ int cme_mlp_fwd2_softmax(const void* A1, const float* W2, const float* b2, const
 
 int cme_mlp_bwd_elem(const void* A1, const float* dz2, const float* W2, void* dZ1, float* gW2,
                      int64_t rows, int H, int ldh, int C, void* stream) {
-    CME_CHECK_ARG(A1 && dz2 && W2 && dZ1 && gW2 && rows >= 0 && H > 0,
-                  "cme_mlp_bwd_elem: bad argument");
+    CME_CHECK_ARG(A1 && dz2 && W2 && dZ1 && rows >= 0 && H > 0, "cme_mlp_bwd_elem: bad argument");
     CME_CHECK_ARG(C == 10, "cme_mlp_bwd_elem: built for 10 classes (got %d)", C);
     CME_CHECK_ARG(ldh % 4 == 0 && ldh >= (H + 3) / 4 * 4, "cme_mlp_bwd_elem: ldh (%d)", ldh);
     if (rows == 0) return 0;
@@ -278,8 +291,24 @@ int cme_mlp_bwd_elem(const void* A1, const float* dz2, const float* W2, void* dZ
     if (rpb < 64) rpb = 64;
     row_blocks = cme::ceil_div64(rows, rpb);
     CME_CHECK_ARG(row_blocks < 65536, "cme_mlp_bwd_elem: too many row blocks");
-    bwd_elem_kernel<10><<<dim3(col_blocks, (unsigned)row_blocks), 256, 0, cme::as_stream(stream)>>>(
-        (const __nv_bfloat16*)A1, dz2, W2, (__nv_bfloat16*)dZ1, gW2, rows, rpb, H, ldh);
+    if (gW2)
+        bwd_elem_kernel<10, true><<<dim3(col_blocks, (unsigned)row_blocks), 256, 0, cme::as_stream(stream)>>>(
+            (const __nv_bfloat16*)A1, dz2, W2, (__nv_bfloat16*)dZ1, gW2, rows, rpb, H, ldh);
+    else
+        bwd_elem_kernel<10, false><<<dim3(col_blocks, (unsigned)row_blocks), 256, 0, cme::as_stream(stream)>>>(
+            (const __nv_bfloat16*)A1, dz2, W2, (__nv_bfloat16*)dZ1, nullptr, rows, rpb, H, ldh);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_f32_to_bf16_2d(const float* src, int ld_src, void* dst_bf16, int ld_dst, int rows, int cols,
+                       void* stream) {
+    CME_CHECK_ARG(src && dst_bf16 && rows >= 0 && cols >= 0 && ld_src >= cols && ld_dst >= cols,
+                  "cme_f32_to_bf16_2d: bad argument");
+    if (rows == 0 || cols == 0) return 0;
+    f32_to_bf16_2d_kernel<<<cme::stride_grid((int64_t)rows * cols, 256, 8), 256, 0,
+                            cme::as_stream(stream)>>>(src, ld_src, (__nv_bfloat16*)dst_bf16, ld_dst,
+                                                      rows, cols);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -181,6 +181,23 @@ int cme_mlp_fwd2_softmax(const void* A1, const float* W2, const float* b2, const
  * zeroed by the caller. */
 int cme_mlp_bwd_elem(const void* A1, const float* dz2, const float* W2, void* dZ1, float* gW2,
                      int64_t rows, int H, int ldh, int C, void* stream);
+/* The same backward pass with gW2 == NULL only produces dZ1 (half the FMA work);
+ * pair it with cme_mlp_dw2_tc. */
+/* Layer 2 on the tensor cores: logits = A1 * W2c^T accumulate in TMEM (N = 16,
+ * K = H, the kernel streams A1 once at HBM speed), and the epilogue does bias,
+ * softmax, cross-entropy, arg-max, dz2 (fp32 rows of 16), dz2b (the same values
+ * as bf16 rows of 64 for cme_mlp_dw2_tc; may be NULL), the b2 gradient and the
+ * loss in registers.  W2c: bf16 [16][ldh], rows >= C zero. */
+int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int32_t* labels,
+                    float* dz2, void* dz2b, float* loss_sum, int32_t* pred, float* gb2, float scale,
+                    int64_t rows, int H, int ldh, int C, void* stream);
+/* gW2[c][h] += sum_r dz2b[r][c] * A1[r][h] on the tensor cores (stream-K over the
+ * batch, result tile stored transposed).  gW2 must be zeroed first. */
+int cme_mlp_dw2_tc(const void* A1, const void* dz2b, float* gW2, int64_t rows, int H, int ldh, int C,
+                   void* stream);
+/* fp32 [rows][ld_src] -> bf16 [rows][ld_dst], first `cols` columns (W2 -> W2c). */
+int cme_f32_to_bf16_2d(const float* src, int ld_src, void* dst_bf16, int ld_dst, int rows, int cols,
+                       void* stream);
 /* tcgen05 GEMM #2: gW1[h][k] += sum_r dZ1[r][h] * X[r][k]  (fp32 reductions into
  * gW1, H x K with ld = ldg), both operands MN-major, stream-K balanced over all
  * SMs.  Column K-1 (the ones column) receives the b1 gradient.  Replaces K3

@@ -34,9 +34,14 @@ steps = {
     "stage_u8_to_bf16": lambda: eng.stage(x.data_ptr(), rows),
     "zero_grads": lambda: eng.grads.tensor.zero_(),
     "fwd1_tcgen05": lambda: dev.mlp_fwd1(eng.xb, eng.w1c.tensor, eng.a1, rows, eng.K, eng.Hh),
-    "fwd2_softmax": lambda: dev.mlp_fwd2_softmax(eng.a1, w2, b2, lab, eng.dz2, None, eng.pred, gb2,
+    "fwd2_softmax_simt": lambda: dev.mlp_fwd2_softmax(eng.a1, w2, b2, lab, eng.dz2, None, eng.pred, gb2,
                                                  1.0 / rows, rows, eng.Hh),
-    "bwd_elem": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, gw2, rows, eng.Hh),
+    "fwd2_tc_softmax": lambda: dev.mlp_fwd2_tc(eng.a1, eng.w2c, b2, lab, eng.dz2, eng.dz2b, None, eng.pred, gb2,
+                                               1.0 / rows, rows, eng.Hh),
+    "bwd_elem_dz1_only": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, None, rows, eng.Hh),
+    "dw2_tc": lambda: dev.mlp_dw2_tc(eng.a1, eng.dz2b, gw2, rows, eng.Hh),
+    "recast_w2": lambda: eng._recast_w2(),
+    "bwd_elem_simt": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, gw2, rows, eng.Hh),
     "dw1_tcgen05_streamk": lambda: dev.mlp_dw1(eng.dz1, eng.xb, gw1, rows, eng.K, eng.Hh, eng.ldx),
     "allreduce_sgd": lambda: eng.update(0.001, 1e-4),
     "full_step": lambda: eng.step(x.data_ptr(), lab, rows, 0.001, 1e-4, rows),

@@ -250,3 +250,52 @@ def test_fwd2_softmax_and_bwd_elem(dev, rows, H):
     assert (got_dZ1 - want_dZ1).abs().max() <= 1e-2 * want_dZ1.abs().max() + 1e-9
     want_gW2 = want_dz2.T @ a
     assert (gW2.cpu() - want_gW2).abs().max() < 1e-4 * max(1.0, float(want_gW2.abs().max()))
+
+
+@pytest.mark.parametrize("rows,H", [(50, 100), (1000, 1024), (700, 2500), (4096, 8192)])
+def test_tensor_core_tail_fwd2_and_dw2(dev, rows, H):
+    """Layer 2 + softmax epilogue and the dW2 product on tcgen05 vs fp32 PyTorch."""
+    C = 10
+    ldh = (H + 63) // 64 * 64
+    g = torch.Generator().manual_seed(H + rows)
+    A1 = torch.full((rows, ldh), 0.5, dtype=torch.bfloat16)      # pad columns hold sigmoid(0)
+    A1[:, :H] = torch.rand((rows, H), generator=g).to(torch.bfloat16)
+    W2 = (0.1 * torch.randn((C, H), generator=g)).float()
+    b2 = torch.randn(C, generator=g).float()
+    labels = torch.randint(0, C, (rows,), generator=g).int()
+    scale = 1.0 / rows
+    dW2 = W2.cuda()
+    w2c = torch.zeros((16, ldh), dtype=torch.bfloat16, device="cuda")
+    dev.f32_to_bf16_2d(dW2, H, w2c, ldh, C, H)
+    assert torch.equal(w2c[:C, :H].float().cpu(), W2.bfloat16().float())
+    assert float(w2c[C:].float().abs().max()) == 0.0
+    dz2 = torch.zeros((rows, 16), device="cuda")
+    dz2b = torch.zeros((rows, 64), dtype=torch.bfloat16, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    pred = torch.zeros(rows, dtype=torch.int32, device="cuda")
+    gb2 = torch.zeros(C, device="cuda")
+    dA1 = A1.cuda()
+    dev.mlp_fwd2_tc(dA1, w2c, b2.cuda(), labels.cuda(), dz2, dz2b, loss, pred, gb2, scale, rows, H)
+    z = A1[:, :H].float() @ W2.bfloat16().float().T + b2
+    p = torch.softmax(z, dim=1)
+    want_dz2 = (p - torch.nn.functional.one_hot(labels.long(), C)) * scale
+    assert (dz2[:, :C].cpu() - want_dz2).abs().max() < 2e-3 * scale + 1e-7
+    assert float(dz2[:, C:].abs().max()) == 0.0
+    assert torch.equal(dz2b[:, :16].float().cpu(), dz2.cpu().bfloat16().float())
+    want_loss = -torch.log(p[torch.arange(rows), labels.long()]).sum()
+    assert abs(float(loss.item()) - float(want_loss)) < 2e-3 * max(1.0, float(want_loss))
+    agree = (pred.cpu().long() == z.argmax(dim=1)).double().mean()
+    assert agree > 0.995
+    assert (gb2.cpu() - want_dz2.sum(dim=0)).abs().max() < 1e-4
+
+    gW2 = torch.zeros((C, H), device="cuda")
+    dev.mlp_dw2_tc(dA1, dz2b, gW2, rows, H)
+    want_gW2 = dz2b[:, :C].float().cpu().T @ A1[:, :H].float()
+    err = (gW2.cpu() - want_gW2).abs().max() / want_gW2.abs().max()
+    assert err < 1e-3, float(err)
+    # dZ1-only backward pass
+    dZ1 = torch.zeros((rows, ldh), dtype=torch.bfloat16, device="cuda")
+    dev.mlp_bwd_elem(dA1, dz2, dW2, dZ1, None, rows, H)
+    a = A1[:, :H].float()
+    want_dZ1 = (dz2[:, :C].cpu() @ W2) * a * (1 - a)
+    assert (dZ1[:, :H].float().cpu() - want_dZ1).abs().max() <= 1e-2 * want_dZ1.abs().max() + 1e-9
