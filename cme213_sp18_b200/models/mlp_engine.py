@@ -58,6 +58,7 @@ class MLPEngineBF16:
         self.dz2 = torch.zeros((max_rows, 16), dtype=torch.float32, device=d)
         self.dz2b = torch.zeros((max_rows, 64), dtype=torch.bfloat16, device=d)   # bf16 copy for dW2
         self.w2c = torch.zeros((16, self.ldh), dtype=torch.bfloat16, device=d)    # bf16 W2, rows >= C zero
+        self.w2t = torch.zeros((self.Hp, 64), dtype=torch.bfloat16, device=d)     # bf16 W2^T, 16 live columns
         self.pred = torch.zeros(max_rows, dtype=torch.int32, device=d)
         self.loss = torch.zeros(1, dtype=torch.float32, device=d)
         self.use_mc = False
@@ -95,7 +96,7 @@ class MLPEngineBF16:
 
     def _recast_w2(self) -> None:
         _, w2, _ = self._views(self.params.tensor)
-        dev.f32_to_bf16_2d(w2, self.Hh, self.w2c, self.ldh, self.C, self.Hh)
+        dev.mlp_recast_w2(w2, self.w2c, self.w2t, self.Hh, self.C)
 
     # ---- one minibatch slice ----
     def stage(self, x_u8_ptr: int, rows: int) -> None:
@@ -120,7 +121,7 @@ class MLPEngineBF16:
         _, w2, _ = self._views(self.params.tensor)
         gw1, gw2, _ = self._views(self.grads.tensor)
         if self.tail == "tc":
-            dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, None, rows, self.Hh, self.C)
+            dev.mlp_bwd_dz1_tc(self.a1, self.dz2b, self.w2t, self.dz1, rows, self.Hh)
             dev.mlp_dw2_tc(self.a1, self.dz2b, gw2, rows, self.Hh, self.C)
         else:
             dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, gw2, rows, self.Hh, self.C)

@@ -286,6 +286,19 @@ def mlp_fwd2_tc(A1, W2c, b2, labels, dz2, dz2b, loss_sum, pred, gb2, scale: floa
     _count()
 
 
+def mlp_bwd_dz1_tc(A1, dz2b, W2T, dZ1, rows: int, H: int) -> None:
+    """dZ1 = (dz2 @ W2) * a * (1 - a) on tcgen05, streaming A1 through a TMA staging ring."""
+    check(device_lib().cme_mlp_bwd_dz1_tc(ptr(A1), ptr(dz2b), ptr(W2T), ptr(dZ1), rows, H, A1.shape[1],
+                                          stream_ptr()), "cme_mlp_bwd_dz1_tc")
+    _count()
+
+
+def mlp_recast_w2(W2, w2c, w2t, H: int, C: int = 10) -> None:
+    check(device_lib().cme_mlp_recast_w2(ptr(W2), ptr(w2c), w2c.shape[1], ptr(w2t), H, C, stream_ptr()),
+          "cme_mlp_recast_w2")
+    _count()
+
+
 def mlp_dw2_tc(A1, dz2b, gW2, rows: int, H: int, C: int = 10) -> None:
     check(device_lib().cme_mlp_dw2_tc(ptr(A1), ptr(dz2b), ptr(gW2), rows, H, A1.shape[1], C,
                                       stream_ptr()), "cme_mlp_dw2_tc")

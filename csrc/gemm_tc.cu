@@ -444,6 +444,183 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // =============================================================================
+// Backward through the sigmoid: dZ1 = (dz2 * W2) .* a .* (1 - a)
+// =============================================================================
+// The product has K = 16 (the classes), so one MMA fills a 128 x 256 TMEM tile and
+// the kernel is a stream over A1: the producer lane prefetches A1 chunks
+// (128 rows x 64 columns, TMA, 128-byte swizzle) into a ring of staging buffers,
+// the epilogue warps combine them with the accumulator in place and hand the
+// buffers to TMA stores.  Replaces the CUDA-core pass (ref K2 + K10,
+// fpcode/neural_network.cpp:365-378) and keeps HBM as the only limit.
+constexpr int kDzStages = 2;                 // operand stages (tiny operands)
+constexpr int kDzBufs = 6;                   // A1 / dZ1 staging ring
+constexpr int kDzPending = 2;                // TMA stores allowed in flight
+constexpr int kSmemDz = kDzStages * (kABytes + kBBytesMax) + kDzBufs * kStageBytes + 1024 + 512;
+
+struct DzBarriers {
+    uint64_t full[kDzStages];
+    uint64_t empty[kDzStages];
+    uint64_t tmem_full[2];
+    uint64_t tmem_empty[2];
+    uint64_t ld_full[kDzBufs];
+    uint64_t ld_empty[kDzBufs];
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+bwd_dz1_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b  [rows][16 of 64] */,
+               const __grid_constant__ CUtensorMap tmW /* W2T   [H][16 of 64]    */,
+               const __grid_constant__ CUtensorMap tmA1 /* A1   [rows][H] load   */,
+               const __grid_constant__ CUtensorMap tmZ /* dZ1   [rows][H] store  */,
+               int m_tiles, int n_tiles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + kDzStages * kABytes;
+    uint8_t* sC = sB + kDzStages * kBBytesMax;
+    DzBarriers* bars = (DzBarriers*)(sC + kDzBufs * kStageBytes);
+    constexpr int BN = 256;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmD);
+        prefetch_tmap(&tmW);
+        prefetch_tmap(&tmA1);
+        prefetch_tmap(&tmZ);
+        for (int s = 0; s < kDzStages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&bars->tmem_full[a], 1);
+            mbar_init(&bars->tmem_empty[a], 4);
+        }
+        for (int b = 0; b < kDzBufs; ++b) {
+            mbar_init(&bars->ld_full[b], 1);
+            mbar_init(&bars->ld_empty[b], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&bars->tmem_base, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+    const int num_tiles = m_tiles * n_tiles;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0, buf = 0;
+            uint32_t phase = 0, bphase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                mbar_expect_tx(&bars->full[stage], kABytes + kBBytesMax);
+                tma_load_2d(sA + stage * kABytes, &tmD, &bars->full[stage], 0, m0);
+                tma_load_2d(sB + stage * kBBytesMax, &tmW, &bars->full[stage], 0, n0);
+                if (++stage == kDzStages) { stage = 0; phase ^= 1; }
+                for (int c = 0; c < BN / 64; ++c) {
+                    mbar_wait(&bars->ld_empty[buf], bphase ^ 1);
+                    mbar_expect_tx(&bars->ld_full[buf], kStageBytes);
+                    tma_load_2d(sC + buf * kStageBytes, &tmA1, &bars->ld_full[buf], n0 + c * 64, m0);
+                    if (++buf == kDzBufs) { buf = 0; bphase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                mbar_wait(&bars->full[stage], phase);
+                tc_fence_after();
+                const uint64_t da = smem_desc_sw128(smem_u32(sA + stage * kABytes), 16, 1024);
+                const uint64_t db = smem_desc_sw128(smem_u32(sB + stage * kBBytesMax), 16, 1024);
+                umma_bf16(tmem_base + (uint32_t)(acc * BN), da, db, idesc, 0);   // K = 16: one MMA
+                umma_commit(&bars->empty[stage]);
+                umma_commit(&bars->tmem_full[acc]);
+                if (++stage == kDzStages) { stage = 0; phase ^= 1; }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const bool leader = (warp == 2 && lane == 0);
+        int acc = 0, buf = 0;
+        uint32_t acc_phase = 0, bphase = 0;
+        long long chunk_no = 0;            // chunks stored so far (leader bookkeeping)
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            for (int c = 0; c < BN / 64; ++c) {
+                mbar_wait(&bars->ld_full[buf], bphase);
+                uint8_t* stg = sC + buf * kStageBytes;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + (uint32_t)(c * 64 + half * 32), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const int chunk = half * 4 + g;
+                        const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+                        uint4 a4 = *reinterpret_cast<const uint4*>(stg + off);
+                        uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                        uint32_t p[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float a0 = __uint_as_float(aw[e] << 16);
+                            const float a1 = __uint_as_float(aw[e] & 0xffff0000u);
+                            const float g0 = __uint_as_float(v[g * 8 + 2 * e]);
+                            const float g1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                            p[e] = pack_bf16(g0 * a0 * (1.f - a0), g1 * a1 * (1.f - a1));
+                        }
+                        *reinterpret_cast<uint4*>(stg + off) = make_uint4(p[0], p[1], p[2], p[3]);
+                    }
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(1, 128);
+                if (leader) {
+                    tma_store_2d(&tmZ, stg, n0 + c * 64, m0);
+                    tma_store_commit();
+                    // stores older than the last kDzPending have finished reading their
+                    // buffer: give that buffer back to the producer
+                    tma_store_wait_read<kDzPending>();
+                    if (chunk_no >= kDzPending)
+                        mbar_arrive(&bars->ld_empty[(int)((chunk_no - kDzPending) % kDzBufs)]);
+                    ++chunk_no;
+                }
+                if (++buf == kDzBufs) { buf = 0; bphase ^= 1; }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+        if (leader) tma_store_wait_all<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// =============================================================================
 // host side: tensor maps and launches
 // =============================================================================
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -608,6 +785,28 @@ int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int3
     const int grid = std::min(m_tiles, cme::sm_count());
     gemm_kmajor_kernel<2><<<grid, kThreads, kSmemKMajor, cme::as_stream(stream)>>>(
         tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, int64_t rows,
+                       int H, int ldh, void* stream) {
+    CME_CHECK_ARG(A1 && dz2b && W2T && dZ1 && rows > 0 && H > 0, "cme_mlp_bwd_dz1_tc: bad argument");
+    CME_CHECK_ARG(ldh % 8 == 0 && ldh >= H, "cme_mlp_bwd_dz1_tc: ldh (%d)", ldh);
+    CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_bwd_dz1_tc: too many rows");
+    const int m_tiles = (int)((rows + BM - 1) / BM), n_tiles = (H + 255) / 256;
+    CUtensorMap tmD, tmW, tmA1, tmZ;
+    int rc;
+    // both small operands are rows of 64 bf16 with 16 live values: bound the maps at 16
+    if ((rc = make_map(&tmD, dz2b, 16, (uint64_t)rows, 64, 64, BM))) return rc;
+    if ((rc = make_map(&tmW, W2T, 16, (uint64_t)H, 64, 64, 256))) return rc;
+    if ((rc = make_map(&tmA1, A1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BM))) return rc;
+    if ((rc = make_map(&tmZ, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BM))) return rc;
+    if ((rc = opt_in_smem(bwd_dz1_kernel, kSmemDz))) return rc;
+    const long long tiles = (long long)m_tiles * n_tiles;
+    const int grid = (int)std::min<long long>(tiles, cme::sm_count());
+    bwd_dz1_kernel<<<grid, kThreads, kSmemDz, cme::as_stream(stream)>>>(tmD, tmW, tmA1, tmZ, m_tiles,
+                                                                      n_tiles);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -244,6 +244,27 @@ f32_to_bf16_2d_kernel(const float* __restrict__ src, int ld_src, __nv_bfloat16* 
     }
 }
 
+// W2 (fp32 [C][H]) -> both bf16 layouts the tensor-core tail wants, one thread per column h:
+//   w2c[c][h] (K-major rows for the forward product) and w2t[h][c] (16 of 64 columns live,
+//   K-major rows for the dz2*W2 product)
+__global__ void __launch_bounds__(256)
+recast_w2_kernel(const float* __restrict__ W2, __nv_bfloat16* __restrict__ w2c, int ldh,
+                 __nv_bfloat16* __restrict__ w2t, int H, int C) {
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= H) return;
+    float v[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) v[c] = (c < C) ? W2[(size_t)c * H + h] : 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+        if (c < C) w2c[(size_t)c * ldh + h] = __float2bfloat16_rn(v[c]);
+    if (w2t) {
+        uint4* d = reinterpret_cast<uint4*>(w2t + (size_t)h * 64);
+        d[0] = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
+        d[1] = make_uint4(pack2(v[8], v[9]), pack2(v[10], v[11]), pack2(v[12], v[13]), pack2(v[14], v[15]));
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -297,6 +318,15 @@ int cme_mlp_bwd_elem(const void* A1, const float* dz2, const float* W2, void* dZ
     else
         bwd_elem_kernel<10, false><<<dim3(col_blocks, (unsigned)row_blocks), 256, 0, cme::as_stream(stream)>>>(
             (const __nv_bfloat16*)A1, dz2, W2, (__nv_bfloat16*)dZ1, nullptr, rows, rpb, H, ldh);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_recast_w2(const float* W2, void* w2c, int ldh, void* w2t, int H, int C,
+                                 void* stream) {
+    CME_CHECK_ARG(W2 && w2c && H > 0 && C >= 1 && C <= 16 && ldh >= H, "cme_mlp_recast_w2: bad argument");
+    recast_w2_kernel<<<(H + 255) / 256, 256, 0, cme::as_stream(stream)>>>(
+        W2, (__nv_bfloat16*)w2c, ldh, (__nv_bfloat16*)w2t, H, C);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -195,6 +195,15 @@ int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int3
  * batch, result tile stored transposed).  gW2 must be zeroed first. */
 int cme_mlp_dw2_tc(const void* A1, const void* dz2b, float* gW2, int64_t rows, int H, int ldh, int C,
                    void* stream);
+/* dZ1 = (dz2b * W2T^T) .* A1 .* (1 - A1) on the tensor cores: the K = 16 product is
+ * one MMA per 128 x 256 tile, A1 chunks are prefetched by TMA into a staging ring,
+ * combined with the accumulator in place and written back by TMA stores, so the
+ * pass runs at HBM speed.  W2T: bf16 [H][64] with W2T[h][c] = W2[c][h], columns
+ * >= 16 unused.  dz2b: bf16 [rows][64] from cme_mlp_fwd2_tc. */
+int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, int64_t rows,
+                       int H, int ldh, void* stream);
+/* W2 (fp32 [C][H]) -> w2c (bf16 [16][ldh]) and, if not NULL, w2t (bf16 [H][64]). */
+int cme_mlp_recast_w2(const float* W2, void* w2c, int ldh, void* w2t, int H, int C, void* stream);
 /* fp32 [rows][ld_src] -> bf16 [rows][ld_dst], first `cols` columns (W2 -> W2c). */
 int cme_f32_to_bf16_2d(const float* src, int ld_src, void* dst_bf16, int ld_dst, int rows, int cols,
                        void* stream);

@@ -39,6 +39,7 @@ steps = {
     "fwd2_tc_softmax": lambda: dev.mlp_fwd2_tc(eng.a1, eng.w2c, b2, lab, eng.dz2, eng.dz2b, None, eng.pred, gb2,
                                                1.0 / rows, rows, eng.Hh),
     "bwd_elem_dz1_only": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, None, rows, eng.Hh),
+    "bwd_dz1_tc": lambda: dev.mlp_bwd_dz1_tc(eng.a1, eng.dz2b, eng.w2t, eng.dz1, rows, eng.Hh),
     "dw2_tc": lambda: dev.mlp_dw2_tc(eng.a1, eng.dz2b, gw2, rows, eng.Hh),
     "recast_w2": lambda: eng._recast_w2(),
     "bwd_elem_simt": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, gw2, rows, eng.Hh),

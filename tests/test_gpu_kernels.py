@@ -299,3 +299,14 @@ def test_tensor_core_tail_fwd2_and_dw2(dev, rows, H):
     a = A1[:, :H].float()
     want_dZ1 = (dz2[:, :C].cpu() @ W2) * a * (1 - a)
     assert (dZ1[:, :H].float().cpu() - want_dZ1).abs().max() <= 1e-2 * want_dZ1.abs().max() + 1e-9
+    # the same pass on the tensor cores
+    w2t = torch.zeros((ldh, 64), dtype=torch.bfloat16, device="cuda")
+    dev.mlp_recast_w2(dW2, w2c, w2t, H)
+    assert torch.equal(w2t[:H, :C].float().cpu(), W2.T.bfloat16().float())
+    dZ1b = torch.full((rows, ldh), 3.0, dtype=torch.bfloat16, device="cuda")
+    dev.mlp_bwd_dz1_tc(dA1, dz2b, w2t, dZ1b, rows, H)
+    want_tc = (dz2b[:, :C].float().cpu() @ W2.bfloat16().float()) * a * (1 - a)
+    assert (dZ1b[:, :H].float().cpu() - want_tc).abs().max() <= 1e-2 * want_tc.abs().max() + 1e-9
+    h8 = (H + 7) // 8 * 8        # TMA stores clip the inner dimension at 16-byte granularity
+    if ldh > h8:
+        assert float((dZ1b[:, h8:].float() - 3.0).abs().max()) == 0.0   # pad columns are not written
