@@ -11,10 +11,10 @@
 //                 separate sigmoid pass (ref K6).
 //   gemm_mnmajor  G[M,N] += A[Kd,M]^T * B[Kd,N], both operands MN-major, the
 //                 reduction dimension is the (huge) batch.  dW1 = dZ1^T * X.
-//                 Work is split stream-K style: the (tile, k-block) space is cut
-//                 into equal contiguous ranges, one per SM, and partial tiles are
-//                 added with vector fp32 reductions, so 148 SMs stay busy for any
-//                 batch size.  The ones column of X makes column K of the result
+//                 The batch is cut into a few k-chunks and the (k-chunk, m, n)
+//                 items are dealt round-robin to 148 persistent CTAs, n fastest,
+//                 so CTAs running together share operand rows through L2;
+//                 partial tiles are added with vector fp32 reductions.  The ones column of X makes column K of the result
 //                 the bias gradient (ref K7 row sums) for free.
 //
 // Roles per CTA (192 threads): warp 0 = TMA producer (one lane), warp 1 = MMA
@@ -301,12 +301,12 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 }
 
 // =============================================================================
-// MN-major stream-K GEMM with fp32 reduction epilogue
+// MN-major split-K GEMM with fp32 reduction epilogue
 // =============================================================================
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     float* __restrict__ G, int ldg, int M, int N, int m_tiles, int n_tiles,
-                    int kb_total, int BN, uint32_t tmem_cols, int out_transposed) {
+                    int kb_total, int BN, uint32_t tmem_cols, int out_transposed, int ksplit) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
@@ -321,10 +321,12 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     setup(bars, tmem_cols, warp, lane);
     const uint32_t tmem_base = bars->tmem_base;
 
-    // contiguous slice of the (tile, k-block) space owned by this CTA
-    const long long units = (long long)m_tiles * n_tiles * kb_total;
-    const long long u_begin = units * blockIdx.x / gridDim.x;
-    const long long u_end = units * (blockIdx.x + 1) / gridDim.x;
+    // Work items are (k-chunk, m-tile, n-tile) with n fastest, then m, then the k-chunk, handed
+    // out round-robin.  CTAs that run at the same time therefore sit on the same k-chunk: the
+    // n-tiles of one m-tile read the same A rows and every CTA reads the same B rows, so each
+    // operand byte comes out of HBM once and is served to the other CTAs by L2.
+    const int tiles_mn = m_tiles * n_tiles;
+    const int items = tiles_mn * ksplit;
     const int nb_boxes = (BN + 63) / 64;
     const uint32_t b_bytes = (uint32_t)nb_boxes * 64 * BK * 2;
 
@@ -332,11 +334,10 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            long long u = u_begin;
-            while (u < u_end) {
-                const int tile = (int)(u / kb_total);
-                const int kb0 = (int)(u % kb_total);
-                const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+            for (int item = blockIdx.x; item < items; item += gridDim.x) {
+                const int kc = item / tiles_mn, tile = item % tiles_mn;
+                const int kb0 = (int)((long long)kb_total * kc / ksplit);
+                const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
                 const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
@@ -350,7 +351,6 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         tma_load_2d(b + x * 8192, &tmB, &bars->full[stage], n0 + x * 64, kb * BK);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                u += kb1 - kb0;
             }
         }
         __syncwarp();
@@ -359,10 +359,10 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const uint32_t idesc = idesc_bf16(BM, BN, 1, 1);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            long long u = u_begin;
-            while (u < u_end) {
-                const int kb0 = (int)(u % kb_total);
-                const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+            for (int item = blockIdx.x; item < items; item += gridDim.x) {
+                const int kc = item / tiles_mn;
+                const int kb0 = (int)((long long)kb_total * kc / ksplit);
+                const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
                 mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
@@ -385,7 +385,6 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 umma_commit(&bars->tmem_full[acc]);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
-                u += kb1 - kb0;
             }
         }
         __syncwarp();
@@ -393,11 +392,8 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int q = warp & 3;
         int acc = 0;
         uint32_t acc_phase = 0;
-        long long u = u_begin;
-        while (u < u_end) {
-            const int tile = (int)(u / kb_total);
-            const int kb0 = (int)(u % kb_total);
-            const int kb1 = (int)min((long long)kb_total, kb0 + (u_end - u));
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int tile = item % tiles_mn;
             const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
@@ -437,7 +433,6 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
-            u += kb1 - kb0;
         }
     }
     teardown(bars, tmem_cols, warp);
@@ -670,6 +665,21 @@ int make_map(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
     return 0;
 }
 
+// Number of k-chunks for the (k-chunk, m, n) schedule: the smallest split (at most 16, at least
+// 8 k-blocks per chunk) whose item count fills `sms` CTAs with the least idle tail.
+int choose_ksplit(int tiles_mn, int kb_total, int sms) {
+    int best = 1;
+    double best_eff = 0.0;
+    for (int s = 1; s <= 16; ++s) {
+        if (s > 1 && kb_total / s < 8) break;
+        const long long items = (long long)tiles_mn * s;
+        const long long waves = (items + sms - 1) / sms;
+        const double eff = (double)items / (double)(waves * sms);
+        if (eff > best_eff + 0.02) { best_eff = eff; best = s; }
+    }
+    return best;
+}
+
 uint32_t pow2_cols(int need) {
     uint32_t c = 32;
     while ((int)c < need) c <<= 1;
@@ -758,10 +768,11 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
     if ((rc = make_map(&tmA, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BK))) return rc;
     if ((rc = make_map(&tmB, X, (uint64_t)K, (uint64_t)rows, (uint64_t)ldx, 64, BK))) return rc;
     if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
-    const long long units = (long long)m_tiles * n_tiles * kb_total;
-    const int grid = (int)std::min<long long>(units, cme::sm_count());
+    const int ksplit = choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
+    const long long items = (long long)m_tiles * n_tiles * ksplit;
+    const int grid = (int)std::min<long long>(items, cme::sm_count());
     gemm_mnmajor_kernel<<<grid, kThreads, kSmemMNMajor, cme::as_stream(stream)>>>(
-        tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u, 0);
+        tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u, 0, ksplit);
     CME_LAUNCH_CHECK();
     return 0;
 }
@@ -826,11 +837,12 @@ int cme_mlp_dw2_tc(const void* A1, const void* dz2b, float* gW2, int64_t rows, i
     // zero-filled on chip and never read from memory
     if ((rc = make_map(&tmB, dz2b, 16, (uint64_t)rows, 64, 64, BK))) return rc;
     if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
-    const long long units = (long long)m_tiles * kb_total;
-    const int grid = (int)std::min<long long>(units, cme::sm_count());
+    const int ksplit = choose_ksplit(m_tiles, kb_total, cme::sm_count());
+    const long long items = (long long)m_tiles * ksplit;
+    const int grid = (int)std::min<long long>(items, cme::sm_count());
     // result tile is [h][c]; store it transposed into gW2[c][h]
     gemm_mnmajor_kernel<<<grid, kThreads, kSmemMNMajor, cme::as_stream(stream)>>>(
-        tmA, tmB, gW2, H, H, C, m_tiles, 1, kb_total, 16, 512u, 1);
+        tmA, tmB, gW2, H, H, C, m_tiles, 1, kb_total, 16, 512u, 1, ksplit);
     CME_LAUNCH_CHECK();
     return 0;
 }

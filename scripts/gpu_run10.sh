@@ -1,0 +1,6 @@
+set -x
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_mlp_gpu.py -q -m "gpu and not multigpu" --timeout 120 -x 2>&1 | tail -5
+timeout 600 python scripts/profile_step.py --out gpurun_out/step_wide_v5.json 2>&1 | grep -E "dw1|dw2|full_step|fwd1_tc|cublas"
+timeout 600 python scripts/profile_step.py --rows 8192 --out gpurun_out/step_wide_8192_v5.json 2>&1 | grep -E "dw1|dw2|full_step|fwd1_tc|cublas"
