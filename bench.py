@@ -37,10 +37,12 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="wide", choices=sorted(CONFIGS))
-    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--comm", default="fused", choices=["fused", "mc", "nccl"],
+                    help="fused = peer loads/stores in the update kernel, mc = NVSwitch multimem variant, nccl = library baseline")
     ap.add_argument("--lr", type=float, default=0.001)
     ap.add_argument("--reg", type=float, default=1e-4)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel separately")
     return ap.parse_args()
 
 
@@ -72,8 +74,13 @@ def run_ours(args) -> dict:
     x_host = torch.randint(0, 256, (pool * gb, D), generator=g, dtype=torch.uint8)
     lab_host = torch.randint(0, H[2], (pool * gb,), generator=g, dtype=torch.int32)
 
-    trainer = DataParallelTrainer(H, gb, info, precision="bf16", comm=args.comm, data_mode="sharded")
+    trainer = DataParallelTrainer(H, gb, info, precision="bf16",
+                                  comm="fused" if args.comm == "mc" else args.comm, data_mode="sharded")
     eng = trainer.engine
+    if args.comm == "mc":
+        if not eng.grads.multicast_ptr:
+            raise SystemExit("--comm mc: symmetric memory reports no multicast address on this box")
+        eng.use_mc = True
     nn = M.NeuralNetwork(H)
     eng.load_params(nn)
     # this rank's slices of every pooled minibatch, resident on the device as uint8
@@ -83,14 +90,20 @@ def run_ours(args) -> dict:
 
     def one_step(i):
         p = i % pool
-        eng.step(x_dev[p].data_ptr(), l_dev[p], in_proc, args.lr, args.reg, in_proc * world)
+        eng.step(x_dev[p].data_ptr(), l_dev[p], in_proc, args.lr, args.reg, in_proc * world,
+                 graph=not args.no_graph)
 
+    if not args.no_graph:
+        for p in range(pool):          # set-up: the first visit of each pooled minibatch records its graph
+            one_step(p)
+    sampler = ClockSampler(info.local_rank, period_ms=20).start() if rank == 0 else None
     for i in range(W):
         one_step(i)
     torch.cuda.synchronize()
     barrier(info)
     torch.cuda.synchronize()
-    sampler = ClockSampler(info.local_rank).start() if rank == 0 else None
+    if sampler:
+        sampler.mark()
     launches0 = dev.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -109,7 +122,7 @@ def run_ours(args) -> dict:
     e2e = None
     if not args.no_e2e:
         xp, lp = x_host.pin_memory(), lab_host.pin_memory()
-        feeder = StreamingFeeder(eng, D)
+        feeder = StreamingFeeder(eng, D, graph=not args.no_graph)
         loss_pinned = torch.zeros(max(W, K), dtype=torch.float32).pin_memory()
         batches = lambda n, off: [(((off + i) % pool) * gb, in_proc) for i in range(n)]  # noqa: E731
         feeder.run(xp, lp, batches(W, 0), args.lr, args.reg, world, rank, loss_pinned)
@@ -140,7 +153,8 @@ def run_ours(args) -> dict:
                    "l2": "per-step working set (activations) exceeds L2; inputs rotate over "
                          f"{pool} distinct minibatches" if args.config == "wide"
                          else f"inputs rotate over {pool} distinct minibatches (working set fits L2)",
-                   "optimizer": "sgd+l2 fused with the gradient all-reduce"},
+                   "optimizer": "sgd+l2 fused with the gradient all-reduce",
+                   "launch": "eager" if args.no_graph else "one CUDA graph per step"},
         "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
         "tflops": value * M.flops_per_sample(H) / 1e12,
     }

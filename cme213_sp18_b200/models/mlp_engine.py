@@ -62,6 +62,7 @@ class MLPEngineBF16:
         self.pred = torch.zeros(max_rows, dtype=torch.int32, device=d)
         self.loss = torch.zeros(1, dtype=torch.float32, device=d)
         self.use_mc = False
+        self._graphs = {}                         # CUDA graphs of whole steps, keyed by their arguments
         if self.info.world > 1:
             dist.barrier()                        # every rank's buffers are zeroed before use
 
@@ -156,17 +157,46 @@ class MLPEngineBF16:
         if self.tail == "tc":
             self._recast_w2()
 
-    def step(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
-             norm: float, want_loss: bool = False) -> None:
-        """One training step on `rows` local samples; `norm` = global sample count of the
-        minibatch (in_proc * P, ref fpcode/neural_network.cpp:330-334)."""
-        if rows > self.max_rows:
-            raise ValueError(f"step: {rows} rows exceed the engine capacity {self.max_rows}")
+    def _step_body(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
+                   norm: float, want_loss: bool) -> None:
         self.stage(x_u8_ptr, rows)
         self.grads.tensor.zero_()
+        if want_loss:
+            self.loss.zero_()
         self.forward(rows, labels, 1.0 / norm, want_loss=want_loss)
         self.backward(rows)
         self.update(lr, reg)
+
+    def step(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
+             norm: float, want_loss: bool = False, graph: bool = False) -> None:
+        """One training step on `rows` local samples; `norm` = global sample count of the
+        minibatch (in_proc * P, ref fpcode/neural_network.cpp:330-334).  With want_loss the summed
+        cross-entropy of this step is left in `self.loss`.
+
+        graph=True replays the step as one CUDA graph: the first call with a given argument set
+        runs eagerly and records the launch sequence (staging, memset, the tensor-core kernels,
+        the flag barriers with their device-side epochs and the fused all-reduce), later calls
+        submit the whole step with a single launch.  Every pointer is part of the key, so callers
+        should cycle through a small set of staging buffers."""
+        if rows > self.max_rows:
+            raise ValueError(f"step: {rows} rows exceed the engine capacity {self.max_rows}")
+        if not graph or self.comm == "nccl":
+            self._step_body(x_u8_ptr, labels, rows, lr, reg, norm, want_loss)
+            return
+        key = (x_u8_ptr, labels.data_ptr(), rows, lr, reg, norm, want_loss)
+        entry = self._graphs.get(key)
+        if entry is not None:
+            entry[0].replay()
+            dev._count(entry[1])
+            return
+        self._step_body(x_u8_ptr, labels, rows, lr, reg, norm, want_loss)     # the real step
+        before = dev.launches()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._step_body(x_u8_ptr, labels, rows, lr, reg, norm, want_loss)  # recorded, not run
+        n = dev.launches() - before
+        dev._count(-n)
+        self._graphs[key] = (g, n)
 
     def predict(self, x_u8: torch.Tensor) -> torch.Tensor:
         """Arg-max classes for [n, D] uint8 images on the device (chunks of max_rows)."""

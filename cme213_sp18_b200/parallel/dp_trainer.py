@@ -100,6 +100,7 @@ class DataParallelTrainer:
         self.data = None
         self.labels = None
         self.N = 0
+        self.graph = True          # replay whole steps as CUDA graphs (one per minibatch position)
 
     def set_data(self, X_u8: torch.Tensor | None, labels: torch.Tensor | None) -> None:
         """Upload the dataset once.  In "owner" mode only rank 0 needs to pass tensors."""
@@ -148,10 +149,8 @@ class DataParallelTrainer:
                     lo = start + info.rank * in_proc
                     lab = self.labels[lo: lo + in_proc]
                     if self.precision == "bf16":
-                        if want_loss:
-                            eng.loss.zero_()
                         eng.step(self._data_base + lo * D, lab, in_proc, lr, reg, in_proc * world,
-                                 want_loss=want_loss)
+                                 want_loss=want_loss, graph=self.graph)
                     else:
                         src = self.data if not isinstance(self.data, SymmetricTensor) else None
                         if src is None:
@@ -223,9 +222,10 @@ class StreamingFeeder:
     step i+1 overlaps the compute of step i, and reads the previous step's loss back into pinned
     host memory.  This is the "call a user makes" path that the end-to-end benchmark times."""
 
-    def __init__(self, engine, D: int):
+    def __init__(self, engine, D: int, graph: bool = True):
         self.eng = engine
         self.D = D
+        self.graph = graph
         d = engine.info.device
         self.copy_stream = torch.cuda.Stream(device=d)
         self.xbuf = [torch.empty((engine.max_rows, D), dtype=torch.uint8, device=d) for _ in range(2)]
@@ -265,9 +265,8 @@ class StreamingFeeder:
             if i + 1 < len(batches):
                 self.prefetch(slot ^ 1, *host_slice(batches[i + 1]))
             cur.wait_event(self.ready[slot])
-            eng.loss.zero_()
             eng.step(self.xbuf[slot].data_ptr(), self.lbuf[slot][:in_proc], in_proc, lr, reg,
-                     in_proc * world, want_loss=True)
+                     in_proc * world, want_loss=True, graph=self.graph)
             self.consumed[slot].record(cur)
             loss_out[i: i + 1].copy_(eng.loss, non_blocking=True)
             self.d2h_bytes += 4

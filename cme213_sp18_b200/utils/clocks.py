@@ -19,6 +19,7 @@ class ClockSampler:
         self.proc = None
         self.lines: list[str] = []
         self._thr = None
+        self._mark = 0
 
     def start(self):
         exe = shutil.which("nvidia-smi")
@@ -40,7 +41,18 @@ class ClockSampler:
         self._thr.start()
         return self
 
+    def mark(self) -> None:
+        """Samples taken before this call (warm-up) are dropped unless nothing comes after."""
+        self._mark = len(self.lines)
+
     def stop(self) -> dict:
+        if self.proc is not None and not self.lines:
+            import time
+
+            for _ in range(100):           # a very short timed region: wait for the first sample
+                if self.lines:
+                    break
+                time.sleep(0.02)
         if self.proc is not None:
             self.proc.terminate()
             try:
@@ -50,7 +62,8 @@ class ClockSampler:
             if self._thr is not None:
                 self._thr.join(timeout=1)
         sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        lines = self.lines[self._mark:] if len(self.lines) > self._mark else self.lines[-3:]
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue

@@ -1,0 +1,8 @@
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_mlp_gpu.py tests/test_workloads_gpu.py -q -m "gpu" --timeout 300 -x 2>&1 | tail -4
+timeout 300 python bench.py --steps 20 --warmup 5 2>&1 | tail -1 | tee gpurun_out/bench_wide_1c.log
+timeout 300 python bench.py --config small --steps 200 --warmup 10 2>&1 | tail -1 | tee gpurun_out/bench_small_1c.log
+TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
+timeout 300 $TR --nproc-per-node 2 --master-port 29611 bench.py --gpus 2 --steps 20 --warmup 5 2>&1 | tail -1 | tee gpurun_out/bench_wide_2c.log
+timeout 300 $TR --nproc-per-node 2 --master-port 29612 bench.py --gpus 2 --config small --steps 200 --warmup 10 2>&1 | tail -1 | tee gpurun_out/bench_small_2c.log
