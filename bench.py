@@ -37,8 +37,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="wide", choices=sorted(CONFIGS))
-    ap.add_argument("--comm", default="fused", choices=["fused", "mc", "nccl"],
-                    help="fused = peer loads/stores in the update kernel, mc = NVSwitch multimem variant, nccl = library baseline")
+    ap.add_argument("--comm", default="fused", choices=["fused", "p2p", "mc", "nccl"],
+                    help="fused = in-kernel all-reduce, multimem from 4 ranks up else peer loads/stores; "
+                         "p2p / mc force one variant; nccl = library baseline")
     ap.add_argument("--lr", type=float, default=0.001)
     ap.add_argument("--reg", type=float, default=1e-4)
     ap.add_argument("--no-e2e", action="store_true")
@@ -74,13 +75,8 @@ def run_ours(args) -> dict:
     x_host = torch.randint(0, 256, (pool * gb, D), generator=g, dtype=torch.uint8)
     lab_host = torch.randint(0, H[2], (pool * gb,), generator=g, dtype=torch.int32)
 
-    trainer = DataParallelTrainer(H, gb, info, precision="bf16",
-                                  comm="fused" if args.comm == "mc" else args.comm, data_mode="sharded")
+    trainer = DataParallelTrainer(H, gb, info, precision="bf16", comm=args.comm, data_mode="sharded")
     eng = trainer.engine
-    if args.comm == "mc":
-        if not eng.grads.multicast_ptr:
-            raise SystemExit("--comm mc: symmetric memory reports no multicast address on this box")
-        eng.use_mc = True
     nn = M.NeuralNetwork(H)
     eng.load_params(nn)
     # this rank's slices of every pooled minibatch, resident on the device as uint8
@@ -149,7 +145,9 @@ def run_ours(args) -> dict:
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "impl": "ours",
         "config": {"model": f"mlp-{H[0]}-{H[1]}-{H[2]}", "global_batch": gb, "seq_len": 1,
-                   "parallelism": f"dp{world}", "comm": args.comm if world > 1 else "local",
+                   "parallelism": f"dp{world}",
+                   "comm": ("nccl" if eng.comm == "nccl" else "fused-multimem" if eng.use_mc else "fused-p2p")
+                   if world > 1 else "local",
                    "l2": "per-step working set (activations) exceeds L2; inputs rotate over "
                          f"{pool} distinct minibatches" if args.config == "wide"
                          else f"inputs rotate over {pool} distinct minibatches (working set fits L2)",

@@ -131,7 +131,7 @@ class DataParallelTrainer:
             self._data_base = int(t.data_ptr())
 
     def train(self, nn, lr: float, reg: float, epochs: int, print_every: int = -1, debug_log=None,
-              log=print) -> dict:
+              log=print, debug: bool = False) -> dict:
         info, eng = self.info, self.engine
         eng.load_params(nn)
         D = self.H[0]
@@ -180,9 +180,10 @@ class DataParallelTrainer:
                         losses.append((it, val / (in_proc * world)))
                         if info.is_main:
                             log(f"Loss at iteration {it} of epoch {_epoch}/{epochs} = {losses[-1][1]}")
-                if debug_log is not None and info.is_main and M.print_flag_for(batch, it, print_every):
-                    eng.store_params(nn)
-                    debug_log.write(nn, it)
+                if debug and M.print_flag_for(batch, it, print_every):
+                    eng.store_params(nn)        # collective: the fp32 master is sharded across ranks
+                    if debug_log is not None and info.is_main:
+                        debug_log.write(nn, it)
                 it += 1
         eng.store_params(nn)
         return {"iterations": it, "losses": losses}
@@ -208,7 +209,7 @@ def parallel_train(nn, X, labels, learning_rate: float = 0.001, reg: float = 0.0
         Xu8 = X if X.dtype == torch.uint8 else X.round().clamp(0, 255).to(torch.uint8)
     trainer.set_data(Xu8, labels)
     out = trainer.train(nn, learning_rate, reg, epochs, print_every=print_every,
-                        debug_log=debug_log if debug else None, log=log)
+                        debug_log=debug_log if debug else None, log=log, debug=bool(debug))
     torch.cuda.synchronize()
     out["seconds"] = time.perf_counter() - t0
     return out

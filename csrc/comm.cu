@@ -63,11 +63,15 @@ allreduce_sgd_p2p_kernel(PeerPtrs pp, int rank, int nranks, int64_t begin, int64
         q.y = p.y - lr * (s.y + reg_for(i + 1, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.y);
         q.z = p.z - lr * (s.z + reg_for(i + 2, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.z);
         q.w = p.w - lr * (s.w + reg_for(i + 3, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.w);
-        const bool in_w1 = i < n_w1;
-        const uint2 qb = make_uint2(pack2(q.x, q.y), pack2(q.z, q.w));
-        for (int r = 0; r < nranks; ++r) {
-            *reinterpret_cast<float4*>(pp.params[r] + i) = q;
-            if (in_w1) *reinterpret_cast<uint2*>(pp.w1c[r] + i) = qb;
+        // The fp32 master of W1 is sharded: only its owner keeps it current (nobody else reads
+        // it between steps).  What every rank needs is the bf16 compute copy of W1 and the small
+        // fp32 tail (W2, b2), so only those cross NVLink.
+        if (i < n_w1) {
+            *reinterpret_cast<float4*>(pp.params[rank] + i) = q;
+            const uint2 qb = make_uint2(pack2(q.x, q.y), pack2(q.z, q.w));
+            for (int r = 0; r < nranks; ++r) *reinterpret_cast<uint2*>(pp.w1c[r] + i) = qb;
+        } else {
+            for (int r = 0; r < nranks; ++r) *reinterpret_cast<float4*>(pp.params[r] + i) = q;
         }
     }
 }
@@ -93,10 +97,12 @@ allreduce_sgd_mc_kernel(const float* __restrict__ mc_grads, float* __restrict__ 
         q.y = p.y - lr * (s.y + reg_for(i + 1, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.y);
         q.z = p.z - lr * (s.z + reg_for(i + 2, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.z);
         q.w = p.w - lr * (s.w + reg_for(i + 3, n_w1, ldx, kreg, w2_begin, w2_end, reg) * p.w);
-        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_params + i),
-                     "f"(q.x), "f"(q.y), "f"(q.z), "f"(q.w)
-                     : "memory");
-        if (i < n_w1) {
+        if (i >= n_w1) {
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_params + i),
+                         "f"(q.x), "f"(q.y), "f"(q.z), "f"(q.w)
+                         : "memory");
+        } else {
+            *reinterpret_cast<float4*>(local_params + i) = q;   // sharded fp32 master, see above
             const float b0 = __uint_as_float(pack2(q.x, q.y)), b1 = __uint_as_float(pack2(q.z, q.w));
             asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc_w1c + i),
                          "f"(b0), "f"(b1)

@@ -220,9 +220,11 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
  * Fused all-reduce + L2 + SGD + bf16 re-cast.  Rank r owns the r-th 1/nranks
  * slice: it sums that slice of every rank's gradient buffer straight from peer
  * memory (fixed rank order), applies  p -= lr * (sum_g + reg * p)  (reg only on
- * W1 columns < kreg and on [w2_begin, w2_end)) and stores the new fp32 value
- * into every rank's parameter replica plus, for the W1 part, the bf16 value
- * into every rank's W1c.  Replaces the four MPI_Allreduce calls and the host
+ * W1 columns < kreg and on [w2_begin, w2_end)).  For the W1 part the new fp32
+ * value is stored only in the owner's master copy (the fp32 master of W1 is
+ * sharded by slice; gather the slices before reading it on the host) and the
+ * bf16 value is stored into every rank's W1c; for the tail (W2, b2) the fp32
+ * value is stored into every rank's replica.  Replaces the four MPI_Allreduce calls and the host
  * SGD (ref fpcode/neural_network.cpp:501-541).  grads/params/w1c are HOST
  * arrays of nranks peer-mapped device pointers.  The caller orders ranks with
  * cme_peer_barrier before (gradients complete) and after (weights visible). */
