@@ -301,6 +301,175 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 }
 
 // =============================================================================
+// K-major GEMM on CTA pairs (cta_group::2): 256 x 256 tiles over two SMs
+// =============================================================================
+// Both 1-CTA GEMMs are limited by operand delivery from L2 to the SMs (ncu: ~15.4 TB/s of
+// L2->SM traffic in both, tensor pipe 55-65 % busy).  A pair of CTAs on one tile halves the B
+// bytes each SM has to receive: CTA r loads its own 128 rows of A and rows r*128.. of the
+// 256-row B tile, the leader issues tcgen05.mma.cta_group::2 with M = 256, and the hardware
+// reads the two halves of B from both CTAs' shared memory.  Each CTA keeps its 128 x 256
+// accumulator in its own TMEM and runs its own epilogue.
+constexpr int kStages2 = 6;
+constexpr int kB2Bytes = 128 * BK * 2;       // this CTA's half of the B tile: 16 KB
+constexpr int kSmemKMajor2 = kStages2 * (kABytes + kB2Bytes) + 2 * kStageBytes + 1024 + 256;
+
+struct Barriers2 {
+    uint64_t full[kStages2];      // used in the leader: TMA bytes of both CTAs
+    uint64_t empty[kStages2];     // one multicast commit per consumption, in both CTAs
+    uint64_t tmem_full[2];        // multicast commit, in both CTAs
+    uint64_t tmem_empty[2];       // used in the leader: 4 epilogue warps x 2 CTAs
+    uint32_t tmem_base;
+};
+
+template <int EPI /* 0 = identity, 1 = sigmoid */>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + kStages2 * kABytes;
+    uint8_t* sC = sB + kStages2 * kB2Bytes;
+    Barriers2* bars = (Barriers2*)(sC + 2 * kStageBytes);
+    constexpr int BN = 256;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t cta = cluster_ctarank();          // 0 = leader
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        prefetch_tmap(&tmC);
+        for (int s = 0; s < kStages2; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&bars->tmem_full[a], 1);
+            mbar_init(&bars->tmem_empty[a], 8);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_2cta(&bars->tmem_base, 512);
+        tmem_relinquish_2cta();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    const int num_tiles = m_tiles * n_tiles;         // tiles of 256 x 256
+    const int nk = (K + BK - 1) / BK;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = pair; tile < num_tiles; tile += npairs) {
+                const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
+                const int n0 = (tile % n_tiles) * BN + (int)cta * 128;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    if (cta == 0) mbar_expect_tx(&bars->full[stage], 2 * (kABytes + kB2Bytes));
+                    tma_load_2d_2cta(sA + stage * kABytes, &tmA, &bars->full[stage], kb * BK, m0);
+                    tma_load_2d_2cta(sB + stage * kB2Bytes, &tmB, &bars->full[stage], kb * BK, n0);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0 && cta == 0) {
+            const uint32_t idesc = idesc_bf16(256, BN, 0, 0);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = pair; tile < num_tiles; tile += npairs) {
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const int kvalid = min(BK, K - kb * BK);
+                    const int nmma = (kvalid + 15) >> 4;
+                    const uint64_t da = smem_desc_sw128(smem_u32(sA + stage * kABytes), 16, 1024);
+                    const uint64_t db = smem_desc_sw128(smem_u32(sB + stage * kB2Bytes), 16, 1024);
+                    for (int j = 0; j < nmma; ++j)
+                        umma_bf16_2cta(d_tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc,
+                                       (kb | j) != 0);
+                    umma_commit_2cta(&bars->empty[stage]);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_2cta(&bars->tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const bool leader = (warp == 2 && lane == 0);
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        int cbuf = 0;
+        for (int tile = pair; tile < num_tiles; tile += npairs) {
+            const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
+            const int n0 = (tile % n_tiles) * BN;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            for (int c = 0; c < BN / 64; ++c) {
+                if (leader) tma_store_wait_read<1>();
+                named_bar_sync(1, 128);
+                uint8_t* stg = sC + cbuf * kStageBytes;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + (uint32_t)(c * 64 + half * 32), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint32_t p[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float x0 = __uint_as_float(v[g * 8 + 2 * e]);
+                            float x1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                            if (EPI == 1) { x0 = sigmoid_fast(x0); x1 = sigmoid_fast(x1); }
+                            p[e] = pack_bf16(x0, x1);
+                        }
+                        const int chunk = half * 4 + g;
+                        const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+                        *reinterpret_cast<uint4*>(stg + off) = make_uint4(p[0], p[1], p[2], p[3]);
+                    }
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(1, 128);
+                if (leader) {
+                    tma_store_2d(&tmC, stg, n0 + c * 64, m0);
+                    tma_store_commit();
+                }
+                cbuf ^= 1;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&bars->tmem_empty[acc]);   // the leader's MMA lane waits for both CTAs
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+        if (leader) tma_store_wait_all<0>();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2cta(tmem_base, 512);
+    }
+}
+
+// =============================================================================
 // MN-major split-K GEMM with fp32 reduction epilogue
 // =============================================================================
 __global__ void __launch_bounds__(kThreads, 1)
@@ -715,6 +884,24 @@ int launch_kmajor(int epi, const void* A, const void* B, void* Cout, int64_t M, 
     if ((rc = make_map(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM))) return rc;
     if ((rc = make_map(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN))) return rc;
     if ((rc = make_map(&tmC, Cout, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, BM))) return rc;
+    // CTA-pair path: full 256-wide column tiles and enough row tiles to keep every pair busy
+    static const bool pairs_off = getenv("CME_NO_PAIRS") != nullptr;
+    if (!pairs_off && N % 256 == 0 && M >= 256 && epi <= 1) {
+        const int m2 = (int)((M + 255) / 256), n2 = N / 256;
+        CUtensorMap tmB2;
+        if ((rc = make_map(&tmB2, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, 128))) return rc;
+        const long long t2 = (long long)m2 * n2;
+        int pairs = (int)std::min<long long>(t2, cme::sm_count() / 2);
+        if (epi == 1) {
+            if ((rc = opt_in_smem(gemm_kmajor2_kernel<1>, kSmemKMajor2))) return rc;
+            gemm_kmajor2_kernel<1><<<2 * pairs, kThreads, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
+        } else {
+            if ((rc = opt_in_smem(gemm_kmajor2_kernel<0>, kSmemKMajor2))) return rc;
+            gemm_kmajor2_kernel<0><<<2 * pairs, kThreads, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
+        }
+        CME_LAUNCH_CHECK();
+        return 0;
+    }
     const uint32_t cols = pow2_cols(2 * BN);
     const long long tiles = (long long)m_tiles * n_tiles;
     const int grid = (int)std::min<long long>(tiles, cme::sm_count());
