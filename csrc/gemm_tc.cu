@@ -312,6 +312,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 constexpr int kStages2 = 6;
 constexpr int kB2Bytes = 128 * BK * 2;       // this CTA's half of the B tile: 16 KB
 constexpr int kSmemKMajor2 = kStages2 * (kABytes + kB2Bytes) + 2 * kStageBytes + 1024 + 256;
+constexpr int kSmemMNMajor2 = kStages2 * (kABytes + kB2Bytes) + 1024 + 256;
 
 struct Barriers2 {
     uint64_t full[kStages2];      // used in the leader: TMA bytes of both CTAs
@@ -605,6 +606,158 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
     }
     teardown(bars, tmem_cols, warp);
+}
+
+// =============================================================================
+// MN-major split-K GEMM on CTA pairs: 256 x 256 tiles, fp32 reduction epilogue
+// =============================================================================
+// Same operand layout as gemm_mnmajor_kernel; the pair covers 256 rows of M (CTA r owns rows
+// r*128..) and 256 columns of N, of which each CTA stages 128.  Items are (k-chunk, m, n) dealt
+// round-robin to the pairs, n fastest.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_mnmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     float* __restrict__ G, int ldg, int M, int N, int m_tiles, int n_tiles,
+                     int kb_total, int ksplit) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + kStages2 * kABytes;
+    Barriers2* bars = (Barriers2*)(sB + kStages2 * kB2Bytes);
+    constexpr int BN = 256;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t cta = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        for (int s = 0; s < kStages2; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&bars->tmem_full[a], 1);
+            mbar_init(&bars->tmem_empty[a], 8);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_2cta(&bars->tmem_base, 512);
+        tmem_relinquish_2cta();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    const int tiles_mn = m_tiles * n_tiles;
+    const int items = tiles_mn * ksplit;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int item = pair; item < items; item += npairs) {
+                const int kc = item / tiles_mn, tile = item % tiles_mn;
+                const int kb0 = (int)((long long)kb_total * kc / ksplit);
+                const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
+                const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
+                const int n0 = (tile % n_tiles) * BN + (int)cta * 128;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    if (cta == 0) mbar_expect_tx(&bars->full[stage], 2 * (kABytes + kB2Bytes));
+                    uint8_t* a = sA + stage * kABytes;
+                    uint8_t* b = sB + stage * kB2Bytes;
+                    tma_load_2d_2cta(a, &tmA, &bars->full[stage], m0, kb * BK);
+                    tma_load_2d_2cta(a + 8192, &tmA, &bars->full[stage], m0 + 64, kb * BK);
+                    tma_load_2d_2cta(b, &tmB, &bars->full[stage], n0, kb * BK);
+                    tma_load_2d_2cta(b + 8192, &tmB, &bars->full[stage], n0 + 64, kb * BK);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0 && cta == 0) {
+            const uint32_t idesc = idesc_bf16(256, BN, 1, 1);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int item = pair; item < items; item += npairs) {
+                const int kc = item / tiles_mn;
+                const int kb0 = (int)((long long)kb_total * kc / ksplit);
+                const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a0 = smem_u32(sA + stage * kABytes);
+                    const uint32_t b0 = smem_u32(sB + stage * kB2Bytes);
+#pragma unroll
+                    for (int j = 0; j < BK / 16; ++j) {
+                        const uint64_t da = smem_desc_sw128(a0 + j * 2048, 8192, 1024);
+                        const uint64_t db = smem_desc_sw128(b0 + j * 2048, 8192, 1024);
+                        umma_bf16_2cta(d_tmem, da, db, idesc, (kb > kb0) || (j > 0));
+                    }
+                    umma_commit_2cta(&bars->empty[stage]);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_2cta(&bars->tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int item = pair; item < items; item += npairs) {
+            const int tile = item % tiles_mn;
+            const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
+            const int n0 = (tile % n_tiles) * BN;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            const int h = m0 + q * 32 + lane;
+            float* grow = G + (size_t)h * ldg;
+            for (int c = 0; c < BN / 16; ++c) {
+                if (n0 + c * 16 >= N) break;          // warp-uniform: nothing left in this row block
+                uint32_t v[16];
+                tmem_ld_32x16(t_row + (uint32_t)(c * 16), v);
+                tmem_ld_wait();
+                if (h < M) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const int d = n0 + c * 16 + g * 4;
+                        if (d + 3 < N) {
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(grow + d),
+                                         "f"(__uint_as_float(v[g * 4])), "f"(__uint_as_float(v[g * 4 + 1])),
+                                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
+                                         : "memory");
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                if (d + e < N) atomicAdd(grow + d + e, __uint_as_float(v[g * 4 + e]));
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&bars->tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_2cta(tmem_base, 512);
+    }
 }
 
 // =============================================================================
@@ -954,6 +1107,20 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
     int rc;
     if ((rc = make_map(&tmA, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BK))) return rc;
     if ((rc = make_map(&tmB, X, (uint64_t)K, (uint64_t)rows, (uint64_t)ldx, 64, BK))) return rc;
+    // CTA-pair path for big problems: 256 x 256 tiles (columns past K are masked in the epilogue)
+    static const bool pairs_off = getenv("CME_NO_PAIRS") != nullptr;
+    if (!pairs_off && H >= 512 && K >= 256 && kb_total >= 16) {
+        const int m2 = (H + 255) / 256, n2 = (K + 255) / 256;
+        const int npairs = cme::sm_count() / 2;
+        const int ks = choose_ksplit(m2 * n2, kb_total, npairs);
+        if ((rc = opt_in_smem(gemm_mnmajor2_kernel, kSmemMNMajor2))) return rc;
+        const long long items2 = (long long)m2 * n2 * ks;
+        const int pairs = (int)std::min<long long>(items2, npairs);
+        gemm_mnmajor2_kernel<<<2 * pairs, kThreads, kSmemMNMajor2, cme::as_stream(stream)>>>(
+            tmA, tmB, gW1, ldg, H, K, m2, n2, kb_total, ks);
+        CME_LAUNCH_CHECK();
+        return 0;
+    }
     if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
     const int ksplit = choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
     const long long items = (long long)m_tiles * n_tiles * ksplit;
