@@ -16,13 +16,7 @@ def pagerank_device(row_ptr: torch.Tensor, edges: torch.Tensor, rank0: torch.Ten
                     inv_deg: torch.Tensor, iterations: int) -> torch.Tensor:
     """`iterations` propagation steps on one GPU, ping-ponging two contrib buffers; returns the
     final rank vector.  No host synchronisation inside."""
-    n = rank0.numel()
-    contrib = [torch.empty_like(rank0), torch.empty_like(rank0)]
+    contrib_a, contrib_b = torch.empty_like(rank0), torch.empty_like(rank0)
     rank = torch.empty_like(rank0)
-    if iterations == 0:
-        return rank0.clone()
-    dev.pagerank_prescale(rank0, inv_deg, contrib[0])
-    for it in range(iterations):
-        dev.pagerank_step(row_ptr, edges.data_ptr(), contrib[it & 1], inv_deg, rank,
-                          contrib[(it + 1) & 1], 0, n, n)
+    dev.pagerank_iterate(row_ptr, edges, rank0, inv_deg, contrib_a, contrib_b, rank, iterations)
     return rank

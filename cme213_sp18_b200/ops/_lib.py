@@ -28,6 +28,7 @@ _DEV_SIGS = {
     "cme_shift_bytes": [P, P, c_size_t, c_u8, c_int, P],
     "cme_pagerank_prescale": [P, P, P, c_i64, P],
     "cme_pagerank_step": [P, P, P, P, P, P, P, c_int, c_i64, c_i64, c_i64, P],
+    "cme_pagerank_iterate": [P, P, P, P, P, P, P, c_int, c_i64, P],
     "cme_pagerank_gen_edges": [P, c_i64, c_i64, c_i64, c_u64, P],
     "cme_heat_step": [P, P, c_int, c_int, c_int, c_float, c_float, c_int, c_int, c_float, P],
     "cme_heat_bc": [P, P, c_int, c_int, c_int, c_float, P],

@@ -22,11 +22,6 @@ __global__ void __launch_bounds__(256) prescale_kernel(const float* __restrict__
         contrib[i] = rank[i] * inv_deg[i];
 }
 
-template <int MAX_PEERS>
-struct PeerList {
-    float* p[MAX_PEERS];
-};
-
 __global__ void __launch_bounds__(256)
 propagate_kernel(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict__ edges,
                  const float* __restrict__ contrib_in, const float* __restrict__ inv_deg,
@@ -105,6 +100,26 @@ int cme_pagerank_step(const int64_t* row_ptr, const uint32_t* edges, const float
         row_ptr, edges, contrib_in, inv_deg, rank_out, contrib_out, peer_contrib, nranks,
         row_begin, row_end, base);
     CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_pagerank_iterate(const int64_t* row_ptr, const uint32_t* edges, const float* rank0,
+                         const float* inv_deg, float* contrib_a, float* contrib_b, float* rank_out,
+                         int iterations, int64_t num_nodes, void* stream) {
+    CME_CHECK_ARG(row_ptr && edges && rank0 && inv_deg && contrib_a && contrib_b && rank_out,
+                  "cme_pagerank_iterate: null buffer");
+    CME_CHECK_ARG(iterations >= 0 && num_nodes > 0, "cme_pagerank_iterate: bad argument");
+    int rc = cme_pagerank_prescale(rank0, inv_deg, contrib_a, num_nodes, stream);
+    if (rc) return rc;
+    float* bufs[2] = {contrib_a, contrib_b};
+    for (int it = 0; it < iterations; ++it) {
+        rc = cme_pagerank_step(row_ptr, edges, bufs[it & 1], inv_deg, rank_out, bufs[(it + 1) & 1],
+                               nullptr, 1, 0, num_nodes, num_nodes, stream);
+        if (rc) return rc;
+    }
+    if (iterations == 0)
+        CME_CUDA(cudaMemcpyAsync(rank_out, rank0, sizeof(float) * (size_t)num_nodes,
+                                 cudaMemcpyDeviceToDevice, cme::as_stream(stream)));
     return 0;
 }
 

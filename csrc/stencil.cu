@@ -5,10 +5,10 @@
 // because the order-8 weights cancel heavily in fp32:
 //   variant 0  one point per thread straight from global memory (ref K16)
 //   variant 1  several rows per thread (ref K17, gpuStencilLoop)
-//   variant 2  register-marching column strips with a shared-memory row for
-//              the x neighbours -- the tiled kernel the reference left as an
-//              empty stub (ref gpuStencil.cu:263-308).  Each input value is
-//              read from global memory once per strip.
+//   variant 2  shared-memory tiles with halo plus register marching along y --
+//              the tiled kernel the reference left as an empty stub (ref
+//              gpuStencil.cu:263-308).  Each input value is read from global
+//              memory once per tile.
 // The border decay (ref BC.h:7-38) can ride in the same launch as extra blocks.
 // The slab kernel adds the multi-GPU piece: edge rows are stored directly into
 // the neighbours' ghost rows over NVLink from inside the sweep.
@@ -142,57 +142,55 @@ sweep_loop(float* __restrict__ next, const float* __restrict__ curr, int gx, int
     }
 }
 
-// ---- variant 2: register marching + shared x row -----------------------------
-// A block owns a strip of TX columns and CH rows.  Each thread owns one column,
-// keeps the 2R+1 vertical neighbours in registers and marches down the strip;
-// the centre row is published to shared memory (double buffered, one barrier
-// per row) so the x neighbours come from on-chip memory.  If push_* pointers
-// are set, the rows listed as edge rows are also stored to a neighbour GPU.
-template <int ORDER, int TX>
-__device__ __forceinline__ void march_strip(float* __restrict__ next,
-                                            const float* __restrict__ curr, int gx, int x0,
-                                            int y_lo, int y_hi, int nx, float xcfl, float ycfl,
-                                            float* __restrict__ push_up, int push_up_rows,
-                                            float* __restrict__ push_down, int push_down_from,
-                                            float* smem) {
-    // rows y are interior-row indices of this (local) grid: grid row = y + R
-    constexpr int R = ORDER / 2;
-    constexpr int W = TX + 2 * R;
-    float* rowbuf[2] = {smem, smem + W};
-    const int tid = threadIdx.x;
-    const int x = x0 + tid;               // interior column index
-    const bool active = x < nx;
-    // threads just right of the interior still carry real (border) columns that
-    // their active neighbours read from the shared row; beyond that, clamp
-    const int xc = min(x, nx + R - 1);
-    const float* col = curr + (size_t)(xc + R);
+// ---- variant 2: shared-memory tile + register marching ---------------------------
+// A block of 256 threads owns a tile of kTX x kTY interior points.  The tile and its
+// halo are staged in shared memory once (one barrier per tile); each thread then owns
+// one column of kRY consecutive rows and marches down it with the 2R+1 vertical
+// neighbours in registers, taking the x neighbours from the shared row.  Per output:
+// one new shared load for the window plus 2R+1 for the row, no global re-reads.  If
+// push_* pointers are set, the rows listed as edge rows are also stored to a
+// neighbour GPU.
+constexpr int kTX = 64, kTY = 64, kRY = 16;   // 64 x 4 threads, 16 rows per thread
 
+template <int ORDER>
+__device__ __forceinline__ void tile_compute(float* __restrict__ next,
+                                             const float* __restrict__ curr, int gx, int gy_local,
+                                             int x0, int y0, int nx, int ny_local, float xcfl,
+                                             float ycfl, float* __restrict__ push_up,
+                                             int push_up_rows, float* __restrict__ push_down,
+                                             int push_down_from, float* smem) {
+    constexpr int R = ORDER / 2;
+    constexpr int W = kTX + 2 * R, HT = kTY + 2 * R;
+    const int tid = threadIdx.x;
+    // interior point (x, y) lives at grid (x + R, y + R): the tile with its halo starts at
+    // grid column x0 and grid row y0
+    for (int i = tid; i < W * HT; i += 256) {
+        const int r = i / W, c = i - r * W;
+        const int gr = y0 + r, gc = x0 + c;
+        smem[i] = (gr < gy_local && gc < gx) ? curr[(size_t)gr * gx + gc] : 0.f;
+    }
+    __syncthreads();
+    const int tx = tid & (kTX - 1), tyg = tid / kTX;
+    const int x = x0 + tx;
+    if (x >= nx) return;
+    const int yb = tyg * kRY;                       // first row of this thread inside the tile
+    const float* colp = smem + (size_t)yb * W + tx + R;
     float win[2 * R + 1];
 #pragma unroll
-    for (int k = 0; k < 2 * R; ++k) win[k + 1] = col[(size_t)gx * (y_lo + k)];
-    // win[1..2R] now hold grid rows y_lo .. y_lo+2R-1; the loop shifts then loads
-
-    for (int y = y_lo; y < y_hi; ++y) {
+    for (int k = 0; k < 2 * R; ++k) win[k + 1] = colp[k * W];
+#pragma unroll
+    for (int i = 0; i < kRY; ++i) {
 #pragma unroll
         for (int k = 0; k < 2 * R; ++k) win[k] = win[k + 1];
-        win[2 * R] = col[(size_t)gx * (y + 2 * R)];
-        float* rb = rowbuf[(y - y_lo) & 1];
-        rb[tid + R] = win[R];
-        // x halo of the centre row: 2R values split over the first 2R threads
-        if (tid < 2 * R) {
-            const int hx = (tid < R) ? (x0 - R + tid) : (x0 + TX + (tid - R));
-            const int gcol = hx + R;                 // grid column
-            const int slot = (tid < R) ? tid : (TX + tid);
-            rb[slot] = (gcol >= 0 && gcol < gx) ? curr[(size_t)gx * (y + R) + gcol] : 0.f;
-        }
-        __syncthreads();
-        if (active) {
+        win[2 * R] = colp[(i + 2 * R) * W];
+        const int y = y0 + yb + i;
+        if (y < ny_local) {
+            const float* rowp = smem + (size_t)(yb + i + R) * W + tx;
             float xv[2 * R + 1];
 #pragma unroll
-            for (int k = 0; k <= 2 * R; ++k) xv[k] = rb[tid + k];
+            for (int k = 0; k <= 2 * R; ++k) xv[k] = rowp[k];
             const float v = combine<ORDER>(xv, win, xcfl, ycfl);
-            const size_t off = (size_t)gx * (y + R) + (x + R);
-            next[off] = v;
+            next[(size_t)gx * (y + R) + (x + R)] = v;
             if (push_up && y < push_up_rows) push_up[(size_t)gx * y + (x + R)] = v;
             if (push_down && y >= push_down_from)
                 push_down[(size_t)gx * (y - push_down_from) + (x + R)] = v;
@@ -200,12 +198,12 @@ __device__ __forceinline__ void march_strip(float* __restrict__ next,
     }
 }
 
-template <int ORDER, int TX, int CH>
-__global__ void __launch_bounds__(TX)
+template <int ORDER>
+__global__ void __launch_bounds__(256)
 sweep_shared(float* __restrict__ next, const float* __restrict__ curr, int gx, int gy, float xcfl,
              float ycfl, int tiles_x, int tiles, int bc, float s) {
     constexpr int R = ORDER / 2;
-    __shared__ float smem[2 * (TX + 2 * R)];
+    __shared__ float smem[(kTX + 2 * R) * (kTY + 2 * R)];
     const int nx = gx - 2 * R, ny = gy - 2 * R;
     if ((int)blockIdx.x >= tiles) {
         if (!bc) return;
@@ -217,20 +215,18 @@ sweep_shared(float* __restrict__ next, const float* __restrict__ curr, int gx, i
         return;
     }
     const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
-    const int y_lo = ty * CH;
-    const int y_hi = min(ny, y_lo + CH);
-    march_strip<ORDER, TX>(next, curr, gx, tx * TX, y_lo, y_hi, nx, xcfl, ycfl, nullptr, 0,
-                           nullptr, 0, smem);
+    tile_compute<ORDER>(next, curr, gx, gy, tx * kTX, ty * kTY, nx, ny, xcfl, ycfl, nullptr, 0,
+                        nullptr, 0, smem);
 }
 
 // ---- multi-GPU slab: sweep + BC + halo push in one launch ---------------------
-template <int ORDER, int TX, int CH>
-__global__ void __launch_bounds__(TX)
+template <int ORDER>
+__global__ void __launch_bounds__(256)
 sweep_slab(float* __restrict__ next, const float* __restrict__ curr,
            float* __restrict__ up_ghost, float* __restrict__ down_ghost, int gx, int rows,
            float xcfl, float ycfl, float s, int is_top, int is_bottom, int tiles_x, int tiles) {
     constexpr int R = ORDER / 2;
-    __shared__ float smem[2 * (TX + 2 * R)];
+    __shared__ float smem[(kTX + 2 * R) * (kTY + 2 * R)];
     const int nx = gx - 2 * R;
     const int gy = rows + 2 * R;
     if ((int)blockIdx.x >= tiles) {
@@ -259,12 +255,10 @@ sweep_slab(float* __restrict__ next, const float* __restrict__ curr,
         return;
     }
     const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
-    const int y_lo = ty * CH;
-    const int y_hi = min(rows, y_lo + CH);
     // my first R rows go to the upper neighbour's bottom ghost rows, my last R
     // rows to the lower neighbour's top ghost rows
-    march_strip<ORDER, TX>(next, curr, gx, tx * TX, y_lo, y_hi, nx, xcfl, ycfl, up_ghost, R,
-                           down_ghost, rows - R, smem);
+    tile_compute<ORDER>(next, curr, gx, gy, tx * kTX, ty * kTY, nx, rows, xcfl, ycfl, up_ghost, R,
+                        down_ghost, rows - R, smem);
 }
 
 template <int ORDER>
@@ -287,11 +281,10 @@ int launch_step(float* next, const float* curr, int gx, int gy, float xcfl, floa
         sweep_loop<ORDER, ROWS><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
             next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles, bc, s);
     } else {
-        constexpr int TX = 256, CH = 64;
-        const int tiles_x = (nx + TX - 1) / TX, tiles_y = (ny + CH - 1) / CH;
+        const int tiles_x = (nx + kTX - 1) / kTX, tiles_y = (ny + kTY - 1) / kTY;
         const int64_t tiles = (int64_t)tiles_x * tiles_y;
         CME_CHECK_ARG(tiles + bc_blocks < INT32_MAX, "cme_heat_step: grid too large");
-        sweep_shared<ORDER, TX, CH><<<(unsigned)(tiles + bc_blocks), TX, 0, st>>>(
+        sweep_shared<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
             next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles, bc, s);
     }
     CME_LAUNCH_CHECK();
@@ -302,13 +295,12 @@ template <int ORDER>
 int launch_slab(float* next, const float* curr, float* up, float* down, int gx, int rows,
                 float xcfl, float ycfl, float s, int is_top, int is_bottom, cudaStream_t st) {
     constexpr int R = ORDER / 2;
-    constexpr int TX = 256, CH = 64;
     const int nx = gx - 2 * R;
-    const int tiles_x = (nx + TX - 1) / TX, tiles_y = (rows + CH - 1) / CH;
+    const int tiles_x = (nx + kTX - 1) / kTX, tiles_y = (rows + kTY - 1) / kTY;
     const int64_t tiles = (int64_t)tiles_x * tiles_y;
     const int bc_blocks = 2 * cme::sm_count();
     CME_CHECK_ARG(tiles + bc_blocks < INT32_MAX, "cme_heat_slab_step: grid too large");
-    sweep_slab<ORDER, TX, CH><<<(unsigned)(tiles + bc_blocks), TX, 0, st>>>(
+    sweep_slab<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
         next, curr, up, down, gx, rows, xcfl, ycfl, s, is_top, is_bottom, tiles_x, (int)tiles);
     CME_LAUNCH_CHECK();
     return 0;

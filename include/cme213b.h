@@ -48,6 +48,12 @@ int cme_pagerank_step(const int64_t* row_ptr, const uint32_t* edges, const float
                       const float* inv_deg, float* rank_out, float* contrib_out,
                       float* const* peer_contrib, int nranks, int64_t row_begin, int64_t row_end,
                       int64_t num_nodes, void* stream);
+/* `iterations` steps on one GPU, ping-ponging contrib_a / contrib_b (n floats each), all
+ * launches issued back to back from native code with no host synchronisation
+ * (ref hw2code/pagerank.cu:59-136 device_graph_iterate).  rank_out gets the result. */
+int cme_pagerank_iterate(const int64_t* row_ptr, const uint32_t* edges, const float* rank0,
+                         const float* inv_deg, float* contrib_a, float* contrib_b, float* rank_out,
+                         int iterations, int64_t num_nodes, void* stream);
 /* Device-side graph generator matching cmeh_pagerank_graph (same splitmix64). */
 int cme_pagerank_gen_edges(uint32_t* edges, int64_t edge_begin, int64_t edge_count,
                            int64_t num_nodes, uint64_t seed, void* stream);
