@@ -58,7 +58,8 @@ def main(argv=None) -> int:
             setattr(p, k, getattr(args, k))
     info = init_distributed()
     rank0 = info.is_main
-    g0 = host.heat_init(p.gx, p.gy, p.dx, p.dy)
+    need_host_grid = not args.no_cpu or args.do_global or args.do_block or args.do_shared
+    g0 = host.heat_init(p.gx, p.gy, p.dx, p.dy) if (need_host_grid and (rank0 or not args.no_cpu)) else None
     ok = True
     ref = None
     if rank0:
@@ -71,7 +72,7 @@ def main(argv=None) -> int:
         print(f"{'CPU':>12} {ms:>12.3f} {p.calc_bytes() / ms / 1e6:>14.2f} {p.real_bytes() / ms / 1e6:>14.2f}")
     variants = [(args.do_global, "global", "Global"), (args.do_block, "loop", "Block"),
                 (args.do_shared, "shared", "Shared")]
-    if rank0:
+    if rank0 and any(on for on, _, _ in variants):
         d0 = torch.from_numpy(g0).cuda()
         for on, variant, name in variants:
             if not on:
@@ -88,17 +89,20 @@ def main(argv=None) -> int:
     if args.do_multi:
         from ..parallel.heat_multi import HeatSlabs
 
+        from ..utils.timing import max_over_ranks_ms
+
         slabs = HeatSlabs(p, info)
-        slabs.load(g0)
+        reload = (lambda: slabs.load(g0)) if g0 is not None and not args.no_cpu else slabs.load_initial
+        reload()
         slabs.run(2)
-        slabs.load(g0)
+        reload()
         t = EventTimer().start()
         slabs.run()
-        ms = t.stop().elapsed_ms()
-        full = slabs.gather()
+        ms = max_over_ranks_ms(t.stop().elapsed_ms())
+        full = slabs.gather() if not args.no_cpu else None      # collective: same decision on every rank
         if rank0:
             name = f"Slabs x{info.world}"
-            if ref is not None:
+            if ref is not None and full is not None:
                 ok &= report(name, full.cpu().numpy(), ref, ms, p, "slabErrors.txt")
             else:
                 print(f"{name:>12} {ms:>12.3f} {p.calc_bytes() / ms / 1e6:>14.2f} {p.real_bytes() / ms / 1e6:>14.2f}")
