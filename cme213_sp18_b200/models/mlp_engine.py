@@ -69,6 +69,10 @@ class MLPEngineBF16:
         if comm == "mc" and self.info.world > 1 and not self.use_mc:
             raise RuntimeError("comm='mc': symmetric memory reports no multicast address on this box")
         self._graphs = {}                         # CUDA graphs of whole steps, keyed by their arguments
+        self.side_stream = torch.cuda.Stream(device=d)
+        self.ev = [torch.cuda.Event() for _ in range(4)]
+        # overlap the all-reduce of the first half of W1 with the second half of the backward pass
+        self.overlap = self.info.world > 1 and self.comm == "fused" and self.Hh >= 1024
         if self.info.world > 1:
             dist.barrier()                        # every rank's buffers are zeroed before use
 
@@ -94,19 +98,23 @@ class MLPEngineBF16:
             dist.barrier()
 
     def gather_master(self) -> None:
-        """The fp32 master of W1 is sharded across ranks by update slice; rebuild the full copy on
-        every rank (zero what is not mine, then a sum all-reduce: x + 0 is exact)."""
+        """The fp32 master of W1 is sharded across ranks (every update range is cut into one slice
+        per rank); rebuild the full copy on every rank: keep what is mine, zero the rest, then a
+        sum all-reduce (x + 0 is exact)."""
         if self.info.world == 1 or self.comm == "nccl":
             return
-        quads = self.n_total // 4
-        b = quads * self.info.rank // self.info.world * 4
-        e = quads * (self.info.rank + 1) // self.info.world * 4
         w1 = self.params.tensor[: self.n_w1]
-        if b > 0:
-            w1[: min(b, self.n_w1)].zero_()
-        if e < self.n_w1:
-            w1[e:].zero_()
-        dist.all_reduce(w1)
+        mine = torch.zeros_like(w1)
+        ranges, _ = self.buckets()
+        for r0, r1 in ranges:
+            quads = (r1 - r0) // 4
+            b = r0 + quads * self.info.rank // self.info.world * 4
+            e = r0 + quads * (self.info.rank + 1) // self.info.world * 4
+            b, e = min(b, self.n_w1), min(e, self.n_w1)
+            if e > b:
+                mine[b:e] = w1[b:e]
+        dist.all_reduce(mine)
+        w1.copy_(mine)
 
     def store_params(self, nn) -> None:
         torch.cuda.synchronize()
@@ -128,10 +136,11 @@ class MLPEngineBF16:
         dev.u8_to_bf16_rows(x_u8_ptr, self.xb, rows, self.D, add_ones=True)
 
     def forward(self, rows: int, labels: torch.Tensor | None, scale: float, want_loss: bool = False,
-                want_grad: bool = True) -> None:
+                want_grad: bool = True, skip_fwd1: bool = False) -> None:
         _, w2, b2 = self._views(self.params.tensor)
         _, _, gb2 = self._views(self.grads.tensor)
-        dev.mlp_fwd1(self.xb, self.w1c.tensor, self.a1, rows, self.K, self.Hh)
+        if not skip_fwd1:
+            dev.mlp_fwd1(self.xb, self.w1c.tensor, self.a1, rows, self.K, self.Hh)
         if self.tail == "tc":
             dev.mlp_fwd2_tc(self.a1, self.w2c, b2, labels, self.dz2 if want_grad else None,
                             self.dz2b if want_grad else None, self.loss if want_loss else None,
@@ -141,54 +150,99 @@ class MLPEngineBF16:
                                  self.loss if want_loss else None, self.pred,
                                  gb2 if want_grad else None, scale, rows, self.Hh, self.C)
 
-    def backward(self, rows: int) -> None:
+    def backward(self, rows: int, h0: int = 0, h1: int | None = None, with_dw2: bool = True) -> None:
+        """Backward for hidden units [h0, h1): dZ1 and dW1 of that column block (pointer offsets
+        into the same buffers), plus dW2 of the whole layer when with_dw2."""
+        h1 = self.Hh if h1 is None else h1
         _, w2, _ = self._views(self.params.tensor)
         gw1, gw2, _ = self._views(self.grads.tensor)
+        hb = h1 - h0
         if self.tail == "tc":
-            dev.mlp_bwd_dz1_tc(self.a1, self.dz2b, self.w2t, self.dz1, rows, self.Hh)
-            dev.mlp_dw2_tc(self.a1, self.dz2b, gw2, rows, self.Hh, self.C)
+            a1_blk, dz1_blk = self.a1[:, h0:], self.dz1[:, h0:]
+            dev.mlp_bwd_dz1_tc(a1_blk, self.dz2b, self.w2t[h0:], dz1_blk, rows, hb, ld=self.ldh)
+            dev.mlp_dw1(dz1_blk, self.xb, gw1[h0:], rows, self.K, hb, self.ldx, ldh=self.ldh)
+            if with_dw2:
+                dev.mlp_dw2_tc(self.a1, self.dz2b, gw2, rows, self.Hh, self.C)
         else:
+            assert h0 == 0 and h1 == self.Hh
             dev.mlp_bwd_elem(self.a1, self.dz2, w2, self.dz1, gw2, rows, self.Hh, self.C)
-        dev.mlp_dw1(self.dz1, self.xb, gw1, rows, self.K, self.Hh, self.ldx)
+            dev.mlp_dw1(self.dz1, self.xb, gw1, rows, self.K, self.Hh, self.ldx)
+
+    def _reduce_range(self, lr: float, reg: float, rng: tuple[int, int], ch: int) -> None:
+        """Barrier, fused all-reduce + L2 + SGD + re-cast of one range of the flat vector, barrier."""
+        info = self.info
+        w2_begin, w2_end = self.o_w2, self.o_w2 + self.C * self.Hh
+        if info.world > 1:
+            dev.peer_barrier(self.pads_dev, info.rank, info.world, ch, 0)      # gradients of the range complete
+        if self.use_mc:
+            dev.allreduce_sgd_mc(self.grads.multicast_ptr, self.params.tensor.data_ptr(),
+                                 self.params.multicast_ptr, self.w1c.multicast_ptr, info.rank,
+                                 info.world, self.n_total, self.n_w1, self.ldx, self.D, w2_begin,
+                                 w2_end, lr, reg, rng)
+        else:
+            dev.allreduce_sgd(self.grads.peer_ptrs, self.params.peer_ptrs, self.w1c.peer_ptrs,
+                              info.rank, self.n_total, self.n_w1, self.ldx, self.D, w2_begin, w2_end,
+                              lr, reg, rng)
+        if info.world > 1:
+            dev.peer_barrier(self.pads_dev, info.rank, info.world, ch + 1, 0)  # new weights visible
 
     def update(self, lr: float, reg: float) -> None:
         """Gradient all-reduce + L2 + SGD + bf16 re-cast (ref fpcode/neural_network.cpp:501-541)."""
-        info = self.info
-        w2_begin, w2_end = self.o_w2, self.o_w2 + self.C * self.Hh
         if self.comm == "nccl":
             # baseline path: library all-reduce, then the same update kernel on local pointers
+            w2_begin, w2_end = self.o_w2, self.o_w2 + self.C * self.Hh
             dist.all_reduce(self.grads.tensor)
             dev.allreduce_sgd([self.grads.tensor.data_ptr()], [self.params.tensor.data_ptr()],
                               [self.w1c.tensor.data_ptr()], 0, self.n_total, self.n_w1, self.ldx,
                               self.D, w2_begin, w2_end, lr, reg)
-            if self.tail == "tc":
-                self._recast_w2()
-            return
-        if info.world > 1:
-            dev.peer_barrier(self.pads_dev, info.rank, info.world, 0, 0)   # all gradients complete
-        if self.use_mc and self.grads.multicast_ptr:
-            dev.allreduce_sgd_mc(self.grads.multicast_ptr, self.params.tensor.data_ptr(),
-                                 self.params.multicast_ptr, self.w1c.multicast_ptr, info.rank,
-                                 info.world, self.n_total, self.n_w1, self.ldx, self.D, w2_begin,
-                                 w2_end, lr, reg)
         else:
-            dev.allreduce_sgd(self.grads.peer_ptrs, self.params.peer_ptrs, self.w1c.peer_ptrs,
-                              info.rank, self.n_total, self.n_w1, self.ldx, self.D, w2_begin, w2_end,
-                              lr, reg)
-        if info.world > 1:
-            dev.peer_barrier(self.pads_dev, info.rank, info.world, 1, 0)   # all weights visible
+            self._reduce_range(lr, reg, (0, self.n_total), 0)
         if self.tail == "tc":
             self._recast_w2()
 
+    def buckets(self):
+        """Update ranges of the flat vector: with overlap, W1 rows [0, Hsplit) form the first
+        bucket (reduced on the side stream while the rest of the backward pass runs)."""
+        if not self.overlap:
+            return [(0, self.n_total)], self.Hh
+        hs = (self.Hh // 2 + 255) // 256 * 256
+        if hs <= 0 or hs >= self.Hh:
+            return [(0, self.n_total)], self.Hh
+        return [(0, hs * self.ldx), (hs * self.ldx, self.n_total)], hs
+
     def _step_body(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
                    norm: float, want_loss: bool) -> None:
+        main = torch.cuda.current_stream()
+        side = self.side_stream
+        # gradient memset on the side stream, hidden under staging + the forward GEMM
+        self.ev[0].record(main)
+        side.wait_event(self.ev[0])
+        with torch.cuda.stream(side):
+            self.grads.tensor.zero_()
+            self.ev[1].record(side)
         self.stage(x_u8_ptr, rows)
-        self.grads.tensor.zero_()
         if want_loss:
             self.loss.zero_()
-        self.forward(rows, labels, 1.0 / norm, want_loss=want_loss)
-        self.backward(rows)
-        self.update(lr, reg)
+        dev.mlp_fwd1(self.xb, self.w1c.tensor, self.a1, rows, self.K, self.Hh)
+        main.wait_event(self.ev[1])
+        self.forward(rows, labels, 1.0 / norm, want_loss=want_loss, skip_fwd1=True)
+        ranges, hs = self.buckets()
+        if len(ranges) == 1 or self.comm == "nccl" or self.tail != "tc":
+            self.backward(rows)
+            self.update(lr, reg)
+            return
+        # bucket 0: hidden units [0, hs) -> its all-reduce + SGD runs on the side stream while the
+        # main stream computes the second half of the backward pass
+        self.backward(rows, 0, hs, with_dw2=False)
+        self.ev[2].record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(self.ev[2])
+            self._reduce_range(lr, reg, ranges[0], 0)
+            self.ev[3].record(side)
+        self.backward(rows, hs, self.Hh, with_dw2=True)
+        self._reduce_range(lr, reg, ranges[1], 2)
+        main.wait_event(self.ev[3])
+        self._recast_w2()
 
     def step(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
              norm: float, want_loss: bool = False, graph: bool = False) -> None:

@@ -294,10 +294,12 @@ def mlp_fwd2_tc(A1, W2c, b2, labels, dz2, dz2b, loss_sum, pred, gb2, scale: floa
     _count()
 
 
-def mlp_bwd_dz1_tc(A1, dz2b, W2T, dZ1, rows: int, H: int) -> None:
-    """dZ1 = (dz2 @ W2) * a * (1 - a) on tcgen05, streaming A1 through a TMA staging ring."""
-    check(device_lib().cme_mlp_bwd_dz1_tc(ptr(A1), ptr(dz2b), ptr(W2T), ptr(dZ1), rows, H, A1.shape[1],
-                                          stream_ptr()), "cme_mlp_bwd_dz1_tc")
+def mlp_bwd_dz1_tc(A1, dz2b, W2T, dZ1, rows: int, H: int, ld: int | None = None) -> None:
+    """dZ1 = (dz2 @ W2) * a * (1 - a) on tcgen05, streaming A1 through a TMA staging ring.
+    A1 / dZ1 may be column-block views of wider buffers: pass their row pitch as ld."""
+    check(device_lib().cme_mlp_bwd_dz1_tc(ptr(A1), ptr(dz2b), ptr(W2T), ptr(dZ1), rows, H,
+                                          ld if ld is not None else A1.shape[1], stream_ptr()),
+          "cme_mlp_bwd_dz1_tc")
     _count()
 
 
@@ -319,9 +321,10 @@ def f32_to_bf16_2d(src, ld_src: int, dst, ld_dst: int, rows: int, cols: int) -> 
     _count()
 
 
-def mlp_dw1(dZ1, X, gW1, rows: int, K: int, H: int, ldg: int) -> None:
-    check(device_lib().cme_mlp_dw1(ptr(dZ1), ptr(X), ptr(gW1), rows, K, H, X.shape[1], dZ1.shape[1],
-                                   ldg, stream_ptr()), "cme_mlp_dw1")
+def mlp_dw1(dZ1, X, gW1, rows: int, K: int, H: int, ldg: int, ldh: int | None = None) -> None:
+    check(device_lib().cme_mlp_dw1(ptr(dZ1), ptr(X), ptr(gW1), rows, K, H, X.shape[1],
+                                   ldh if ldh is not None else dZ1.shape[1], ldg, stream_ptr()),
+          "cme_mlp_dw1")
     _count()
 
 
@@ -333,22 +336,24 @@ def _ptr_table(ptrs):
 
 
 def allreduce_sgd(grad_ptrs, param_ptrs, w1c_ptrs, rank: int, n_total: int, n_w1: int, ldx: int,
-                  kreg: int, w2_begin: int, w2_end: int, lr: float, reg: float) -> None:
+                  kreg: int, w2_begin: int, w2_end: int, lr: float, reg: float,
+                  rng: tuple[int, int] | None = None) -> None:
     """Fused gradient all-reduce + L2 + SGD + bf16 re-cast over peer pointers
     (ref fpcode/neural_network.cpp:501-541)."""
     n = len(grad_ptrs)
     check(device_lib().cme_allreduce_sgd(_ptr_table(grad_ptrs), _ptr_table(param_ptrs),
                                          _ptr_table(w1c_ptrs), rank, n, n_total, n_w1, ldx, kreg,
-                                         w2_begin, w2_end, lr, reg, stream_ptr()), "cme_allreduce_sgd")
+                                         w2_begin, w2_end, lr, reg, *(rng or (0, n_total)), stream_ptr()),
+          "cme_allreduce_sgd")
     _count()
 
 
 def allreduce_sgd_mc(mc_grads: int, local_params: int, mc_params: int, mc_w1c: int, rank: int,
                      nranks: int, n_total: int, n_w1: int, ldx: int, kreg: int, w2_begin: int,
-                     w2_end: int, lr: float, reg: float) -> None:
+                     w2_end: int, lr: float, reg: float, rng: tuple[int, int] | None = None) -> None:
     check(device_lib().cme_allreduce_sgd_mc(mc_grads, local_params, mc_params, mc_w1c, rank, nranks,
                                             n_total, n_w1, ldx, kreg, w2_begin, w2_end, lr, reg,
-                                            stream_ptr()), "cme_allreduce_sgd_mc")
+                                            *(rng or (0, n_total)), stream_ptr()), "cme_allreduce_sgd_mc")
     _count()
 
 

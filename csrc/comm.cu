@@ -160,11 +160,11 @@ peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t 
     for (; i < n16; i += stride) dst[i] = cme::ld_stream_u4(src + i);
 }
 
-int slice_bounds(int64_t n_total, int rank, int nranks, int64_t* b, int64_t* e) {
-    // slices are multiples of 4 floats so every access is a 16-byte vector
-    const int64_t quads = n_total / 4;
-    *b = quads * rank / nranks * 4;
-    *e = quads * (rank + 1) / nranks * 4;
+int slice_bounds(int64_t r_begin, int64_t r_end, int rank, int nranks, int64_t* b, int64_t* e) {
+    // the range [r_begin, r_end) is cut into nranks slices of whole 16-byte vectors
+    const int64_t quads = (r_end - r_begin) / 4;
+    *b = r_begin + quads * rank / nranks * 4;
+    *e = r_begin + quads * (rank + 1) / nranks * 4;
     return 0;
 }
 
@@ -174,7 +174,8 @@ extern "C" {
 
 int cme_allreduce_sgd(float* const* grads_host, float* const* params_host, void* const* w1c_host,
                       int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
-                      int64_t w2_begin, int64_t w2_end, float lr, float reg, void* stream) {
+                      int64_t w2_begin, int64_t w2_end, float lr, float reg, int64_t range_begin,
+                      int64_t range_end, void* stream) {
     CME_CHECK_ARG(grads_host && params_host && w1c_host, "cme_allreduce_sgd: null pointer table");
     CME_CHECK_ARG(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks,
                   "cme_allreduce_sgd: rank %d of %d", rank, nranks);
@@ -187,8 +188,11 @@ int cme_allreduce_sgd(float* const* grads_host, float* const* params_host, void*
         pp.w1c[r] = (__nv_bfloat16*)w1c_host[r];
         CME_CHECK_ARG(pp.grads[r] && pp.params[r] && pp.w1c[r], "cme_allreduce_sgd: null peer %d", r);
     }
+    CME_CHECK_ARG(0 <= range_begin && range_begin <= range_end && range_end <= n_total &&
+                      range_begin % 4 == 0 && range_end % 4 == 0,
+                  "allreduce_sgd: bad range [%lld, %lld)", (long long)range_begin, (long long)range_end);
     int64_t b, e;
-    slice_bounds(n_total, rank, nranks, &b, &e);
+    slice_bounds(range_begin, range_end, rank, nranks, &b, &e);
     if (e <= b) return 0;
     const int grid = cme::stride_grid((e - b) / 4, 256, 4, 2);
     allreduce_sgd_p2p_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
@@ -200,14 +204,17 @@ int cme_allreduce_sgd(float* const* grads_host, float* const* params_host, void*
 int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_params,
                          void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
                          int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
-                         void* stream) {
+                         int64_t range_begin, int64_t range_end, void* stream) {
     CME_CHECK_ARG(mc_grads && local_params && mc_params && mc_w1c, "cme_allreduce_sgd_mc: null pointer");
     CME_CHECK_ARG(nranks >= 1 && rank >= 0 && rank < nranks, "cme_allreduce_sgd_mc: rank %d of %d",
                   rank, nranks);
     CME_CHECK_ARG(n_total % 4 == 0 && n_w1 % 4 == 0 && ldx % 4 == 0 && n_w1 <= n_total,
                   "cme_allreduce_sgd_mc: sizes must be multiples of 4 floats");
+    CME_CHECK_ARG(0 <= range_begin && range_begin <= range_end && range_end <= n_total &&
+                      range_begin % 4 == 0 && range_end % 4 == 0,
+                  "allreduce_sgd: bad range [%lld, %lld)", (long long)range_begin, (long long)range_end);
     int64_t b, e;
-    slice_bounds(n_total, rank, nranks, &b, &e);
+    slice_bounds(range_begin, range_end, rank, nranks, &b, &e);
     if (e <= b) return 0;
     const int grid = cme::stride_grid((e - b) / 4, 256, 4, 2);
     allreduce_sgd_mc_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(

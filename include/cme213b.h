@@ -233,16 +233,20 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
  * value is stored into every rank's replica.  Replaces the four MPI_Allreduce calls and the host
  * SGD (ref fpcode/neural_network.cpp:501-541).  grads/params/w1c are HOST
  * arrays of nranks peer-mapped device pointers.  The caller orders ranks with
- * cme_peer_barrier before (gradients complete) and after (weights visible). */
+ * cme_peer_barrier before (gradients complete) and after (weights visible).
+ * Only [range_begin, range_end) of the flat vector is processed (cut into nranks
+ * slices), so the trainer can reduce one bucket while later gradients are still
+ * being computed; pass 0, n_total for everything. */
 int cme_allreduce_sgd(float* const* grads, float* const* params, void* const* w1c, int rank,
                       int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
-                      int64_t w2_begin, int64_t w2_end, float lr, float reg, void* stream);
+                      int64_t w2_begin, int64_t w2_end, float lr, float reg, int64_t range_begin,
+                      int64_t range_end, void* stream);
 /* Same update through the NVSwitch multicast mapping: multimem.ld_reduce sums in
  * the switch, multimem.st replicates the result to all GPUs. */
 int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_params,
                          void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
                          int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
-                         void* stream);
+                         int64_t range_begin, int64_t range_end, void* stream);
 
 /* Cross-GPU flag barrier over a peer-mapped pad of uint32 slots.  pads: DEVICE
  * array of nranks pointers (one pad per rank, >= 8*64 slots, zero-initialised).
