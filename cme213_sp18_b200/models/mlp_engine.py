@@ -32,6 +32,7 @@ class MLPEngineBF16:
         """tail: "tc" runs layer 2 / dW2 on the tensor cores, "simt" on the CUDA-core kernels."""
         self.info = info or DistInfo(device=torch.device("cuda", torch.cuda.current_device()))
         self.tail = tail
+        self.fused_tail = tail == "tc"            # dZ1 + dW2 in one pass over A1
         self.D, self.Hh, self.C = H
         if self.C != 10:
             raise ValueError("the bf16 engine is built for 10 classes")
@@ -159,9 +160,14 @@ class MLPEngineBF16:
         hb = h1 - h0
         if self.tail == "tc":
             a1_blk, dz1_blk = self.a1[:, h0:], self.dz1[:, h0:]
-            dev.mlp_bwd_dz1_tc(a1_blk, self.dz2b, self.w2t[h0:], dz1_blk, rows, hb, ld=self.ldh)
+            if self.fused_tail:
+                # dZ1 and this column block's share of dW2 in one pass over A1
+                dev.mlp_bwd_tail_tc(a1_blk, self.dz2b, self.w2t[h0:], dz1_blk, gw2[:, h0:], self.Hh,
+                                    rows, hb, ld=self.ldh, C=self.C)
+            else:
+                dev.mlp_bwd_dz1_tc(a1_blk, self.dz2b, self.w2t[h0:], dz1_blk, rows, hb, ld=self.ldh)
             dev.mlp_dw1(dz1_blk, self.xb, gw1[h0:], rows, self.K, hb, self.ldx, ldh=self.ldh)
-            if with_dw2:
+            if with_dw2 and not self.fused_tail:
                 dev.mlp_dw2_tc(self.a1, self.dz2b, gw2, rows, self.Hh, self.C)
         else:
             assert h0 == 0 and h1 == self.Hh

@@ -55,6 +55,7 @@ _DEV_SIGS = {
     "cme_mlp_bwd_elem": [P, P, P, P, P, c_i64, c_int, c_int, c_int, P],
     "cme_mlp_fwd2_tc": [P, P, P, P, P, P, P, P, P, c_float, c_i64, c_int, c_int, c_int, P],
     "cme_mlp_bwd_dz1_tc": [P, P, P, P, c_i64, c_int, c_int, P],
+    "cme_mlp_bwd_tail_tc": [P, P, P, P, P, c_int, c_i64, c_int, c_int, c_int, P],
     "cme_mlp_recast_w2": [P, P, c_int, P, c_int, c_int, P],
     "cme_mlp_dw2_tc": [P, P, P, c_i64, c_int, c_int, c_int, P],
     "cme_f32_to_bf16_2d": [P, c_int, P, c_int, c_int, c_int, P],

@@ -303,6 +303,15 @@ def mlp_bwd_dz1_tc(A1, dz2b, W2T, dZ1, rows: int, H: int, ld: int | None = None)
     _count()
 
 
+def mlp_bwd_tail_tc(A1, dz2b, W2T, dZ1, gW2, ldg2: int, rows: int, H: int, ld: int | None = None,
+                    C: int = 10) -> None:
+    """dZ1 and dW2 in one pass over A1 (fused backward tail on tcgen05)."""
+    check(device_lib().cme_mlp_bwd_tail_tc(ptr(A1), ptr(dz2b), ptr(W2T), ptr(dZ1), ptr(gW2), ldg2, rows, H,
+                                           ld if ld is not None else A1.shape[1], C, stream_ptr()),
+          "cme_mlp_bwd_tail_tc")
+    _count()
+
+
 def mlp_recast_w2(W2, w2c, w2t, H: int, C: int = 10) -> None:
     check(device_lib().cme_mlp_recast_w2(ptr(W2), ptr(w2c), w2c.shape[1], ptr(w2t), H, C, stream_ptr()),
           "cme_mlp_recast_w2")
@@ -367,3 +376,43 @@ def peer_barrier(pads_dev: torch.Tensor, rank: int, nranks: int, channel: int, e
 def peer_copy(src_ptr: int, dst: torch.Tensor, nbytes: int) -> None:
     check(device_lib().cme_peer_copy(src_ptr, ptr(dst), nbytes, stream_ptr()), "cme_peer_copy")
     _count()
+
+
+# ------------------------------------------------------------------ native step executor
+def make_mlp_plan(eng):
+    """ctypes mirror of CmeMlpPlan (include/cme213b.h) for an MLPEngineBF16."""
+    import ctypes as C
+
+    class CmeMlpPlan(C.Structure):
+        _fields_ = [("D", C.c_int), ("H", C.c_int), ("C", C.c_int), ("Hp", C.c_int), ("ldx", C.c_int),
+                    ("ldh", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("max_rows", C.c_int64),
+                    ("params", C.c_void_p * 16), ("grads", C.c_void_p * 16), ("w1c", C.c_void_p * 16),
+                    ("xb", C.c_void_p), ("a1", C.c_void_p), ("dz1", C.c_void_p), ("dz2b", C.c_void_p),
+                    ("w2c", C.c_void_p), ("w2t", C.c_void_p), ("dz2", C.c_void_p), ("pred", C.c_void_p),
+                    ("pads_dev", C.c_void_p)]
+
+    p = CmeMlpPlan()
+    p.D, p.H, p.C, p.Hp, p.ldx, p.ldh = eng.D, eng.Hh, eng.C, eng.Hp, eng.ldx, eng.ldh
+    p.rank, p.nranks, p.max_rows = eng.info.rank, eng.info.world, eng.max_rows
+    for r in range(eng.info.world):
+        p.params[r] = eng.params.peer_ptrs[r]
+        p.grads[r] = eng.grads.peer_ptrs[r]
+        p.w1c[r] = eng.w1c.peer_ptrs[r]
+    p.xb, p.a1, p.dz1, p.dz2b = ptr(eng.xb), ptr(eng.a1), ptr(eng.dz1), ptr(eng.dz2b)
+    p.w2c, p.w2t, p.dz2, p.pred = ptr(eng.w2c), ptr(eng.w2t), ptr(eng.dz2), ptr(eng.pred)
+    p.pads_dev = ptr(eng.pads_dev) if eng.info.world > 1 else None
+    return p
+
+
+def mlp_step_native(plan, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
+                    scale: float, loss_sum: torch.Tensor | None = None) -> None:
+    """The whole step issued by the native executor cme_mlp_step (one C call)."""
+    import ctypes as C
+
+    lib = device_lib()
+    lib.cme_mlp_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
+                                 C.c_float, C.c_void_p, C.c_void_p]
+    lib.cme_mlp_step.restype = C.c_int
+    check(lib.cme_mlp_step(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
+                           stream_ptr()), "cme_mlp_step")
+    _count(9 if plan.nranks == 1 else 11)

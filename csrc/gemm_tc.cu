@@ -938,6 +938,253 @@ bwd_dz1_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b  [rows][16 of 64]
 }
 
 // =============================================================================
+// Fused backward tail: dZ1 = (dz2 * W2) .* a .* (1 - a)  AND  gW2 += dz2^T * A1
+// =============================================================================
+// Both need one pass over A1, so they share it.  A tile is 128 batch rows x 128 hidden
+// columns = two A1 chunks (128 x 64, TMA, 128-byte swizzle) in adjacent staging buffers.
+//   MMA1  g[128 b][128 h] = dz2b[128 b][16] * W2T[128 h][16]^T      (K = 16, one instruction)
+//   MMA2  D2[128 h][16 c] += A1_tile^T[128 h][128 b] * dz2b[128 b][16 c]   (8 instructions)
+// MMA2 reads the A1 chunks as an MN-major operand straight out of the staging ring and
+// the dz2b tile (already in shared memory for MMA1) as its B operand; the epilogue then
+// overwrites the chunks in place with dZ1 and TMA-stores them.  Each CTA walks a
+// contiguous range of tiles in column-major order, so D2 stays in TMEM across all the
+// row tiles of one column block and is flushed (transposed, fp32 reductions) only when
+// the column block changes.
+constexpr int kFtBufs = 8;                    // A1 / dZ1 staging ring, used in aligned pairs
+constexpr int kFtPending = 2;
+constexpr int kFtOpBytes = 128 * 128;         // one 128-row x 64-col bf16 box (16 live columns)
+constexpr int kSmemFt = 2 * kFtOpBytes + kFtOpBytes + kFtBufs * kStageBytes + 1024 + 512;
+
+struct FtBarriers {
+    uint64_t op_full[2], op_empty[2];         // dz2b tile ring
+    uint64_t w_full, w_empty;                 // W2T tile of the current column block
+    uint64_t g_full[2], g_empty[2];           // TMEM g accumulators
+    uint64_t ld_full[kFtBufs], ld_empty[kFtBufs];
+    uint64_t a1_done[kFtBufs / 2];            // MMA2 finished reading a chunk pair
+    uint64_t d2_full, d2_empty;
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+bwd_tail_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b [rows][16 of 64] */,
+                const __grid_constant__ CUtensorMap tmW /* W2T  [H][16 of 64]    */,
+                const __grid_constant__ CUtensorMap tmA1 /* A1  [rows][H] load   */,
+                const __grid_constant__ CUtensorMap tmZ /* dZ1  [rows][H] store  */,
+                float* __restrict__ gW2, int ldg2, int H, int C, int m_tiles, int n_tiles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* sD = smem;                               // 2 x 16 KB: dz2b tiles
+    uint8_t* sW = sD + 2 * kFtOpBytes;                // 16 KB: W2T tile
+    uint8_t* sC = sW + kFtOpBytes;                    // staging ring
+    FtBarriers* bars = (FtBarriers*)(sC + kFtBufs * kStageBytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmD);
+        prefetch_tmap(&tmW);
+        prefetch_tmap(&tmA1);
+        prefetch_tmap(&tmZ);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&bars->op_full[s], 1);
+            mbar_init(&bars->op_empty[s], 1);
+            mbar_init(&bars->g_full[s], 1);
+            mbar_init(&bars->g_empty[s], 4);
+        }
+        mbar_init(&bars->w_full, 1);
+        mbar_init(&bars->w_empty, 1);
+        mbar_init(&bars->d2_full, 1);
+        mbar_init(&bars->d2_empty, 4);
+        for (int b = 0; b < kFtBufs; ++b) {
+            mbar_init(&bars->ld_full[b], 1);
+            mbar_init(&bars->ld_empty[b], 1);
+        }
+        for (int b = 0; b < kFtBufs / 2; ++b) mbar_init(&bars->a1_done[b], 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&bars->tmem_base, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+    constexpr uint32_t kD2Col = 256;                  // g stages at columns 0 and 128, D2 at 256
+
+    // contiguous range of tiles, column block (n) slowest: tile = n * m_tiles + m
+    const long long total = (long long)m_tiles * n_tiles;
+    const long long t_begin = total * blockIdx.x / gridDim.x;
+    const long long t_end = total * (blockIdx.x + 1) / gridDim.x;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0, pair = 0, last_n = -1;
+            uint32_t phase = 0, pphase = 0, wphase = 0;
+            for (long long t = t_begin; t < t_end; ++t) {
+                const int n = (int)(t / m_tiles), m = (int)(t % m_tiles);
+                const int m0 = m * 128, n0 = n * 128;
+                if (n != last_n) {
+                    mbar_wait(&bars->w_empty, wphase ^ 1);
+                    mbar_expect_tx(&bars->w_full, kFtOpBytes);
+                    tma_load_2d(sW, &tmW, &bars->w_full, 0, n0);
+                    wphase ^= 1;
+                    last_n = n;
+                }
+                mbar_wait(&bars->op_empty[stage], phase ^ 1);
+                mbar_expect_tx(&bars->op_full[stage], kFtOpBytes);
+                tma_load_2d(sD + stage * kFtOpBytes, &tmD, &bars->op_full[stage], 0, m0);
+                if (++stage == 2) { stage = 0; phase ^= 1; }
+                for (int c = 0; c < 2; ++c) {
+                    const int buf = pair * 2 + c;
+                    mbar_wait(&bars->ld_empty[buf], pphase ^ 1);
+                    mbar_expect_tx(&bars->ld_full[buf], kStageBytes);
+                    tma_load_2d(sC + buf * kStageBytes, &tmA1, &bars->ld_full[buf], n0 + c * 64, m0);
+                }
+                if (++pair == kFtBufs / 2) { pair = 0; pphase ^= 1; }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_g = idesc_bf16(128, 128, 0, 0);     // dz2b (K-major) x W2T (K-major)
+            const uint32_t idesc_d2 = idesc_bf16(128, 16, 1, 1);     // A1^T (MN-major) x dz2b (MN-major)
+            int stage = 0, acc = 0, pair = 0, last_n = -1;
+            uint32_t phase = 0, acc_phase = 0, pphase = 0, wphase = 0, d2phase = 0;
+            bool d2_open = false;                                    // D2 holds partial sums of last_n
+            for (long long t = t_begin; t < t_end; ++t) {
+                const int n = (int)(t / m_tiles);
+                if (n != last_n) {
+                    if (d2_open) {                                   // finish the previous column block
+                        umma_commit(&bars->d2_full);
+                        d2_open = false;
+                    }
+                    mbar_wait(&bars->w_full, wphase);
+                    wphase ^= 1;
+                    mbar_wait(&bars->d2_empty, d2phase ^ 1);         // previous flush has drained D2
+                    d2phase ^= 1;
+                    last_n = n;
+                }
+                mbar_wait(&bars->op_full[stage], phase);
+                mbar_wait(&bars->g_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_addr = smem_u32(sD + stage * kFtOpBytes);
+                umma_bf16(tmem_base + (uint32_t)(acc * 128), smem_desc_sw128(d_addr, 16, 1024),
+                          smem_desc_sw128(smem_u32(sW), 16, 1024), idesc_g, 0);
+                umma_commit(&bars->g_full[acc]);
+                // the W2T tile may be replaced once the last MMA1 of this column block is done
+                const bool last_of_n = (t + 1 == t_end) || ((int)((t + 1) / m_tiles) != n);
+                if (last_of_n) umma_commit(&bars->w_empty);
+                // MMA2 over the 128 batch rows of this tile
+                mbar_wait(&bars->ld_full[pair * 2], pphase);
+                mbar_wait(&bars->ld_full[pair * 2 + 1], pphase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sC + pair * 2 * kStageBytes);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint64_t da = smem_desc_sw128(a_addr + j * 2048, kStageBytes, 1024);
+                    const uint64_t db = smem_desc_sw128(d_addr + j * 2048, 8192, 1024);
+                    umma_bf16(tmem_base + kD2Col, da, db, idesc_d2, (d2_open || j > 0) ? 1u : 0u);
+                }
+                d2_open = true;
+                umma_commit(&bars->a1_done[pair]);
+                umma_commit(&bars->op_empty[stage]);
+                if (++stage == 2) { stage = 0; phase ^= 1; }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                if (++pair == kFtBufs / 2) { pair = 0; pphase ^= 1; }
+            }
+            if (d2_open) umma_commit(&bars->d2_full);
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const bool leader = (warp == 2 && lane == 0);
+        int acc = 0, pair = 0;
+        uint32_t acc_phase = 0, pphase = 0, d2phase = 0;
+        long long chunk_no = 0;
+        for (long long t = t_begin; t < t_end; ++t) {
+            const int n = (int)(t / m_tiles), m = (int)(t % m_tiles);
+            const int m0 = m * 128, n0 = n * 128;
+            mbar_wait(&bars->g_full[acc], acc_phase);
+            mbar_wait(&bars->a1_done[pair], pphase);      // MMA2 no longer reads the pair
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 128);
+            for (int c = 0; c < 2; ++c) {
+                const int buf = pair * 2 + c;
+                mbar_wait(&bars->ld_full[buf], pphase);
+                uint8_t* stg = sC + buf * kStageBytes;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_row + (uint32_t)(c * 64 + half * 32), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const int chunk = half * 4 + g;
+                        const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+                        uint4 a4 = *reinterpret_cast<const uint4*>(stg + off);
+                        uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                        uint32_t p[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float a0 = __uint_as_float(aw[e] << 16);
+                            const float a1 = __uint_as_float(aw[e] & 0xffff0000u);
+                            const float g0 = __uint_as_float(v[g * 8 + 2 * e]);
+                            const float g1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                            p[e] = pack_bf16(g0 * a0 * (1.f - a0), g1 * a1 * (1.f - a1));
+                        }
+                        *reinterpret_cast<uint4*>(stg + off) = make_uint4(p[0], p[1], p[2], p[3]);
+                    }
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(1, 128);
+                if (leader) {
+                    tma_store_2d(&tmZ, stg, n0 + c * 64, m0);
+                    tma_store_commit();
+                    tma_store_wait_read<kFtPending>();
+                    if (chunk_no >= kFtPending)
+                        mbar_arrive(&bars->ld_empty[(int)((chunk_no - kFtPending) % kFtBufs)]);
+                    ++chunk_no;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->g_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+            if (++pair == kFtBufs / 2) { pair = 0; pphase ^= 1; }
+            // last tile of this column block: flush D2 = gW2^T block, transposed
+            const bool last_of_n = (t + 1 == t_end) || ((int)((t + 1) / m_tiles) != n);
+            if (last_of_n) {
+                mbar_wait(&bars->d2_full, d2phase);
+                d2phase ^= 1;
+                tc_fence_after();
+                uint32_t v[16];
+                tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + kD2Col, v);
+                tmem_ld_wait();
+                const int h = n0 + row;
+                if (h < H) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c)
+                        if (c < C) atomicAdd(gW2 + (size_t)c * ldg2 + h, __uint_as_float(v[c]));
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars->d2_empty);
+            }
+        }
+        if (leader) tma_store_wait_all<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// =============================================================================
 // host side: tensor maps and launches
 // =============================================================================
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -1172,6 +1419,28 @@ int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* 
     const int grid = (int)std::min<long long>(tiles, cme::sm_count());
     bwd_dz1_kernel<<<grid, kThreads, kSmemDz, cme::as_stream(stream)>>>(tmD, tmW, tmA1, tmZ, m_tiles,
                                                                       n_tiles);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
+                        int ldg2, int64_t rows, int H, int ldh, int C, void* stream) {
+    CME_CHECK_ARG(A1 && dz2b && W2T && dZ1 && gW2 && rows > 0 && H > 0, "cme_mlp_bwd_tail_tc: bad argument");
+    CME_CHECK_ARG(ldh % 8 == 0 && ldh >= H && C >= 1 && C <= 16, "cme_mlp_bwd_tail_tc: ldh (%d), C (%d)", ldh, C);
+    CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_bwd_tail_tc: too many rows");
+    const int m_tiles = (int)((rows + 127) / 128), n_tiles = (H + 127) / 128;
+    CUtensorMap tmD, tmW, tmA1, tmZ;
+    int rc;
+    if ((rc = make_map(&tmD, dz2b, 16, (uint64_t)rows, 64, 64, 128))) return rc;
+    if ((rc = make_map(&tmW, W2T, 16, (uint64_t)H, 64, 64, 128))) return rc;
+    if ((rc = make_map(&tmA1, A1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, 128))) return rc;
+    if ((rc = make_map(&tmZ, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, 128))) return rc;
+    if ((rc = opt_in_smem(bwd_tail_kernel, kSmemFt))) return rc;
+    const long long tiles = (long long)m_tiles * n_tiles;
+    const int grid = (int)std::min<long long>(tiles, cme::sm_count());
+    CME_CHECK_ARG(ldg2 >= H, "cme_mlp_bwd_tail_tc: ldg2 (%d) < H (%d)", ldg2, H);
+    bwd_tail_kernel<<<grid, kThreads, kSmemFt, cme::as_stream(stream)>>>(tmD, tmW, tmA1, tmZ, gW2, ldg2,
+                                                                        H, C, m_tiles, n_tiles);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -208,6 +208,13 @@ int cme_mlp_dw2_tc(const void* A1, const void* dz2b, float* gW2, int64_t rows, i
  * >= 16 unused.  dz2b: bf16 [rows][64] from cme_mlp_fwd2_tc. */
 int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, int64_t rows,
                        int H, int ldh, void* stream);
+/* cme_mlp_bwd_dz1_tc and cme_mlp_dw2_tc in ONE pass over A1: every 128 x 128 tile of A1 is
+ * staged once, used as the MN-major operand of the dW2 product (accumulated in TMEM across
+ * the row tiles of a column block) and then overwritten in place with dZ1.  gW2 rows have
+ * pitch ldg2 (>= H) so a column block of a wider layer can be processed; gW2 must be zeroed
+ * first.  Replaces ref K2 + K10 + K3(dW2) (fpcode/neural_network.cpp:357-378). */
+int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
+                        int ldg2, int64_t rows, int H, int ldh, int C, void* stream);
 /* W2 (fp32 [C][H]) -> w2c (bf16 [16][ldh]) and, if not NULL, w2t (bf16 [H][64]). */
 int cme_mlp_recast_w2(const float* W2, void* w2c, int ldh, void* w2t, int H, int C, void* stream);
 /* fp32 [rows][ld_src] -> bf16 [rows][ld_dst], first `cols` columns (W2 -> W2c). */
@@ -247,6 +254,35 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
                          void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
                          int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
                          int64_t range_begin, int64_t range_end, void* stream);
+
+/* ---- native step executor ------------------------------------------------------
+ * Every device buffer of one rank's bf16 engine.  D inputs, H hidden units, C classes;
+ * ldx = (D+1) rounded up to 64, Hp = ldh = H rounded up to 64.  params / grads are the
+ * flat fp32 vectors described above, one pointer per rank (peer-mapped for nranks > 1);
+ * w1c: bf16 [Hp][ldx] per rank.  Local scratch: xb bf16 [max_rows][ldx], a1 and dz1 bf16
+ * [max_rows][ldh], dz2 fp32 [max_rows][16], dz2b bf16 [max_rows][64] (zero-initialised),
+ * pred int32 [max_rows], w2c bf16 [16][ldh] and w2t bf16 [Hp][64] (zero-initialised).
+ * pads_dev: device array of per-rank flag pads (see cme_peer_barrier), NULL for one rank. */
+typedef struct CmeMlpPlan {
+    int D, H, C, Hp, ldx, ldh;
+    int rank, nranks;
+    int64_t max_rows;
+    float* params[16];
+    float* grads[16];
+    void* w1c[16];
+    void *xb, *a1, *dz1, *dz2b, *w2c, *w2t;
+    float* dz2;
+    int32_t* pred;
+    uint32_t* const* pads_dev;
+} CmeMlpPlan;
+/* One whole training step on `rows` local samples (uint8 pixels x_u8 [rows][D], labels
+ * int32 [rows], both device pointers; x_u8 may be peer-mapped): staging, forward, backward,
+ * fused all-reduce + L2 + SGD, bf16 re-cast, all on `stream` with no host synchronisation.
+ * scale = 1 / (global samples in the minibatch); loss_sum (may be NULL) += cross-entropy.
+ * The C++ counterpart of one iteration of parallel_train's loop
+ * (ref fpcode/neural_network.cpp:484-541). */
+int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
+                 float lr, float reg, float scale, float* loss_sum, void* stream);
 
 /* Cross-GPU flag barrier over a peer-mapped pad of uint32 slots.  pads: DEVICE
  * array of nranks pointers (one pad per rank, >= 8*64 slots, zero-initialised).

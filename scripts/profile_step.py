@@ -40,6 +40,7 @@ steps = {
                                                1.0 / rows, rows, eng.Hh),
     "bwd_elem_dz1_only": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, None, rows, eng.Hh),
     "bwd_dz1_tc": lambda: dev.mlp_bwd_dz1_tc(eng.a1, eng.dz2b, eng.w2t, eng.dz1, rows, eng.Hh),
+    "bwd_tail_fused_dz1_dw2": lambda: dev.mlp_bwd_tail_tc(eng.a1, eng.dz2b, eng.w2t, eng.dz1, gw2, eng.Hh, rows, eng.Hh),
     "dw2_tc": lambda: dev.mlp_dw2_tc(eng.a1, eng.dz2b, gw2, rows, eng.Hh),
     "recast_w2": lambda: eng._recast_w2(),
     "bwd_elem_simt": lambda: dev.mlp_bwd_elem(eng.a1, eng.dz2, w2, eng.dz1, gw2, rows, eng.Hh),

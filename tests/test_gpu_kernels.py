@@ -310,3 +310,10 @@ def test_tensor_core_tail_fwd2_and_dw2(dev, rows, H):
     h8 = (H + 7) // 8 * 8        # TMA stores clip the inner dimension at 16-byte granularity
     if ldh > h8:
         assert float((dZ1b[:, h8:].float() - 3.0).abs().max()) == 0.0   # pad columns are not written
+    # dZ1 and dW2 fused into one pass
+    dZ1f = torch.full((rows, ldh), 3.0, dtype=torch.bfloat16, device="cuda")
+    gW2f = torch.zeros((C, H), device="cuda")
+    dev.mlp_bwd_tail_tc(dA1, dz2b, w2t, dZ1f, gW2f, H, rows, H)
+    assert torch.equal(dZ1f[:, :H], dZ1b[:, :H])
+    errf = (gW2f.cpu() - want_gW2).abs().max() / want_gW2.abs().max()
+    assert errf < 1e-3, float(errf)

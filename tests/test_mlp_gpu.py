@@ -95,6 +95,31 @@ def test_fp64_engine_grade_tolerance(hidden, tmp_path):
     assert rep["passed"], rep
 
 
+def test_native_step_executor_matches_python_engine():
+    """cme_mlp_step (one C call per step) against the Python-issued launch sequence."""
+    from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+    from cme213_sp18_b200.ops import device as dev
+
+    H, rows = [784, 300, 10], 1000
+    x, lab = mnist.synthetic_mnist(rows, seed=8, pixel_max=1)
+    nn = M.NeuralNetwork(H)
+    xd, ld = x.cuda(), lab.cuda()
+    a, b = MLPEngineBF16(H, rows, _info()), MLPEngineBF16(H, rows, _info())
+    a.load_params(nn)
+    b.load_params(nn)
+    plan = dev.make_mlp_plan(b)
+    loss_b = torch.zeros(1, device="cuda")
+    for _ in range(3):
+        a.step(xd.data_ptr(), ld, rows, 0.5, 1e-4, rows, want_loss=True)
+        loss_b.zero_()
+        dev.mlp_step_native(plan, xd.data_ptr(), ld, rows, 0.5, 1e-4, 1.0 / rows, loss_b)
+    torch.cuda.synchronize()
+    # fp32 reductions land in a different order run to run: compare with a tolerance
+    d = (a.params.tensor - b.params.tensor).abs().max() / a.params.tensor.abs().max()
+    assert float(d) < 1e-4, float(d)
+    assert abs(float(a.loss.item()) - float(loss_b.item())) < 1e-3 * float(a.loss.item())
+
+
 def _torchrun(script: Path, nproc: int, port: int, timeout: int = 300):
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     return subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
