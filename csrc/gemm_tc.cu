@@ -39,12 +39,14 @@ constexpr int BK = 64;                       // bf16 elements = one 128-byte swi
 constexpr int kABytes = BM * BK * 2;         // 16 KB
 constexpr int kBBytesMax = 256 * BK * 2;     // 32 KB
 constexpr int kStageBytes = 64 * 128 * 2;    // 128 rows x 64 cols bf16 epilogue staging
-constexpr int kSmemKMajor = kStages * (kABytes + kBBytesMax) + 2 * kStageBytes + 1024 + 256;
-constexpr int kSmemMNMajor = kStages * (kABytes + kBBytesMax) + 1024 + 256;
+constexpr int kSmemKMajor = kStages * (kABytes + kBBytesMax) + 2 * kStageBytes + 1024 + 512;
+constexpr int kSmemSoftmax = 10 * (kABytes + 16 * BK * 2) + 1024 + 512;
+constexpr int kSmemMNMajor = kStages * (kABytes + kBBytesMax) + 1024 + 512;
 
+constexpr int kMaxStages = 10;
 struct Barriers {
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
     uint32_t tmem_base;
@@ -54,9 +56,10 @@ __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
     return (uint8_t*)(((uintptr_t)p + 1023) & ~(uintptr_t)1023);
 }
 
-__device__ __forceinline__ void setup(Barriers* bars, uint32_t tmem_cols, int warp, int lane) {
+__device__ __forceinline__ void setup(Barriers* bars, uint32_t tmem_cols, int warp, int lane,
+                                      int stages = kStages) {
     if (warp == 0 && lane == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < stages; ++s) {
             mbar_init(&bars->full[s], 1);
             mbar_init(&bars->empty[s], 1);
         }
@@ -107,12 +110,17 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                    const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K, int BN,
                    uint32_t tmem_cols, SoftmaxEpi sm) {
+    // The softmax variant (EPI == 2) has a 16-row B tile and no output staging: it spends its
+    // shared memory on a deep ring instead (10 x 18 KB in flight per SM), because it is a pure
+    // stream over A and per-SM bandwidth is set by the bytes in flight.
+    constexpr int S = (EPI == 2) ? kMaxStages : kStages;
+    constexpr int kBSlot = (EPI == 2) ? 16 * BK * 2 : kBBytesMax;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
-    uint8_t* sB = sA + kStages * kABytes;
-    uint8_t* sC = sB + kStages * kBBytesMax;
-    Barriers* bars = (Barriers*)(sC + 2 * kStageBytes);
+    uint8_t* sB = sA + S * kABytes;
+    uint8_t* sC = sB + S * kBSlot;
+    Barriers* bars = (Barriers*)(sC + (EPI == 2 ? 0 : 2 * kStageBytes));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
@@ -120,7 +128,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         prefetch_tmap(&tmB);
         if (EPI != 2) prefetch_tmap(&tmC);
     }
-    setup(bars, tmem_cols, warp, lane);
+    setup(bars, tmem_cols, warp, lane, S);
     const uint32_t tmem_base = bars->tmem_base;
 
     const int num_tiles = m_tiles * n_tiles;
@@ -138,8 +146,8 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     mbar_wait(&bars->empty[stage], phase ^ 1);
                     mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
                     tma_load_2d(sA + stage * kABytes, &tmA, &bars->full[stage], kb * BK, m0);
-                    tma_load_2d(sB + stage * kBBytesMax, &tmB, &bars->full[stage], kb * BK, n0);
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    tma_load_2d(sB + stage * kBSlot, &tmB, &bars->full[stage], kb * BK, n0);
+                    if (++stage == S) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -160,14 +168,14 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     const int kvalid = min(BK, K - kb * BK);
                     const int nmma = (kvalid + 15) >> 4;
                     const uint64_t da = smem_desc_sw128(smem_u32(sA + stage * kABytes), 16, 1024);
-                    const uint64_t db = smem_desc_sw128(smem_u32(sB + stage * kBBytesMax), 16, 1024);
+                    const uint64_t db = smem_desc_sw128(smem_u32(sB + stage * kBSlot), 16, 1024);
                     for (int j = 0; j < nmma; ++j) {
                         // +32 bytes per 16-element K step inside the 128-byte swizzle row
                         umma_bf16(d_tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc,
                                   (kb | j) != 0);
                     }
                     umma_commit(&bars->empty[stage]);
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    if (++stage == S) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(&bars->tmem_full[acc]);
                 acc ^= 1;
@@ -1392,10 +1400,10 @@ int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int3
     // the K extent is the true H: pad columns of A1 hold sigmoid(0) and must read as zero
     if ((rc = make_map(&tmA, A1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, BK, BM))) return rc;
     if ((rc = make_map(&tmB, W2c, (uint64_t)H, 16, (uint64_t)ldh, BK, 16))) return rc;
-    if ((rc = opt_in_smem(gemm_kmajor_kernel<2>, kSmemKMajor))) return rc;
+    if ((rc = opt_in_smem(gemm_kmajor_kernel<2>, kSmemSoftmax))) return rc;
     SoftmaxEpi sm{b2, labels, dz2, (__nv_bfloat16*)dz2b, loss_sum, pred, gb2, scale, (long long)rows, C};
     const int grid = std::min(m_tiles, cme::sm_count());
-    gemm_kmajor_kernel<2><<<grid, kThreads, kSmemKMajor, cme::as_stream(stream)>>>(
+    gemm_kmajor_kernel<2><<<grid, kThreads, kSmemSoftmax, cme::as_stream(stream)>>>(
         tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm);
     CME_LAUNCH_CHECK();
     return 0;
