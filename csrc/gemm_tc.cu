@@ -40,7 +40,7 @@ constexpr int kABytes = BM * BK * 2;         // 16 KB
 constexpr int kBBytesMax = 256 * BK * 2;     // 32 KB
 constexpr int kStageBytes = 64 * 128 * 2;    // 128 rows x 64 cols bf16 epilogue staging
 constexpr int kSmemKMajor = kStages * (kABytes + kBBytesMax) + 2 * kStageBytes + 1024 + 512;
-constexpr int kSmemSoftmax = 10 * (kABytes + 16 * BK * 2) + 1024 + 512;
+constexpr int kSmemSoftmax = 10 * (kABytes + 16 * BK * 2) + 1024 + 512 + 128 * 16 * 4;
 constexpr int kSmemMNMajor = kStages * (kABytes + kBBytesMax) + 1024 + 512;
 
 constexpr int kMaxStages = 10;
@@ -49,6 +49,7 @@ struct Barriers {
     uint64_t empty[kMaxStages];
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
+    uint64_t x_full, x_empty;     // split-K exchange between the two CTAs of a cluster (softmax kernel)
     uint32_t tmem_base;
 };
 
@@ -67,6 +68,8 @@ __device__ __forceinline__ void setup(Barriers* bars, uint32_t tmem_cols, int wa
             mbar_init(&bars->tmem_full[a], 1);
             mbar_init(&bars->tmem_empty[a], 4);   // one arrive per epilogue warp
         }
+        mbar_init(&bars->x_full, 4);
+        mbar_init(&bars->x_empty, 4);
         fence_barrier_init();
     }
     if (warp == 1) {   // whole warp: .sync.aligned
@@ -109,7 +112,7 @@ template <int EPI /* 0 = identity, 1 = sigmoid, 2 = bias + softmax + cross-entro
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                    const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K, int BN,
-                   uint32_t tmem_cols, SoftmaxEpi sm) {
+                   uint32_t tmem_cols, SoftmaxEpi sm, int ksplit) {
     // The softmax variant (EPI == 2) has a 16-row B tile and no output staging: it spends its
     // shared memory on a deep ring instead (10 x 18 KB in flight per SM), because it is a pure
     // stream over A and per-SM bandwidth is set by the bytes in flight.
@@ -134,15 +137,26 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const int num_tiles = m_tiles * n_tiles;
     const int nk = (K + BK - 1) / BK;
     const uint32_t b_bytes = (uint32_t)BN * BK * 2;
+    // ksplit == 2 (softmax kernel, few row tiles): the two CTAs of a cluster take the two halves
+    // of K for the same row tile; CTA 1 hands its partial logits to CTA 0 through distributed
+    // shared memory and CTA 0 finishes the row.
+    const uint32_t cta = (EPI == 2 && ksplit == 2) ? cluster_ctarank() : 0u;
+    const int tile_first = (ksplit == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int tile_step = (ksplit == 2) ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int kb_lo = (ksplit == 2) ? (int)cta * (nk / 2) : 0;
+    const int kb_hi = (ksplit == 2 && cta == 0) ? nk / 2 : nk;
+    // 128 x 16 fp32 exchange tile (EPI == 2), 16-byte aligned for the vector stores
+    float* xbuf = reinterpret_cast<float*>(((uintptr_t)(bars + 1) + 15) & ~(uintptr_t)15);
+    if (ksplit == 2) cluster_sync_all();                  // peer barriers are initialised
 
     if (warp == 0) {
         if (lane == 0) {
             // ---------------- TMA producer ----------------
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
                 const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
-                for (int kb = 0; kb < nk; ++kb) {
+                for (int kb = kb_lo; kb < kb_hi; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
                     mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
                     tma_load_2d(sA + stage * kABytes, &tmA, &bars->full[stage], kb * BK, m0);
@@ -158,11 +172,11 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             const uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
                 mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-                for (int kb = 0; kb < nk; ++kb) {
+                for (int kb = kb_lo; kb < kb_hi; ++kb) {
                     mbar_wait(&bars->full[stage], phase);
                     tc_fence_after();
                     const int kvalid = min(BK, K - kb * BK);
@@ -172,7 +186,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                     for (int j = 0; j < nmma; ++j) {
                         // +32 bytes per 16-element K step inside the 128-byte swizzle row
                         umma_bf16(d_tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc,
-                                  (kb | j) != 0);
+                                  (kb > kb_lo) || (j > 0));
                     }
                     umma_commit(&bars->empty[stage]);
                     if (++stage == S) { stage = 0; phase ^= 1; }
@@ -189,9 +203,9 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int row = q * 32 + lane;             // row inside the 128-row tile
         const bool leader = (warp == 2 && lane == 0);
         int acc = 0;
-        uint32_t acc_phase = 0;
+        uint32_t acc_phase = 0, xphase = 0;
         int cbuf = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
             const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
@@ -206,6 +220,34 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                 if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
+                if (ksplit == 2) {
+                    if (cta == 1) {
+                        // hand my half of the K sum to CTA 0 (its buffer is free again once it
+                        // has arrived on my x_empty), then go on to the next tile
+                        mbar_wait_cluster(&bars->x_empty, xphase ^ 1);
+                        const uint32_t dst = map_to_cta(smem_u32(xbuf + row * 16), 0);
+#pragma unroll
+                        for (int k4 = 0; k4 < 4; ++k4)
+                            st_cluster_f4(dst + k4 * 16, __uint_as_float(v[4 * k4]), __uint_as_float(v[4 * k4 + 1]),
+                                          __uint_as_float(v[4 * k4 + 2]), __uint_as_float(v[4 * k4 + 3]));
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&bars->x_full), 0));
+                        xphase ^= 1;
+                        continue;
+                    }
+                    mbar_wait_cluster(&bars->x_full, xphase);
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; ++k4) {
+                        const float4 o = *reinterpret_cast<const float4*>(xbuf + row * 16 + 4 * k4);
+                        v[4 * k4] = __float_as_uint(__uint_as_float(v[4 * k4]) + o.x);
+                        v[4 * k4 + 1] = __float_as_uint(__uint_as_float(v[4 * k4 + 1]) + o.y);
+                        v[4 * k4 + 2] = __float_as_uint(__uint_as_float(v[4 * k4 + 2]) + o.z);
+                        v[4 * k4 + 3] = __float_as_uint(__uint_as_float(v[4 * k4 + 3]) + o.w);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&bars->x_empty), 1));
+                    xphase ^= 1;
+                }
                 const long long grow = (long long)m0 + row;
                 const bool valid = grow < sm.rows;
                 const int C = sm.classes;
@@ -305,6 +347,7 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         if (EPI != 2 && leader) tma_store_wait_all<0>();
     }
+    if (ksplit == 2) cluster_sync_all();     // nobody leaves while the peer may still touch its smem
     teardown(bars, tmem_cols, warp);
 }
 
@@ -1317,11 +1360,11 @@ int launch_kmajor(int epi, const void* A, const void* B, void* Cout, int64_t M, 
     if (epi == 1) {
         if ((rc = opt_in_smem(gemm_kmajor_kernel<1>, kSmemKMajor))) return rc;
         gemm_kmajor_kernel<1><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
-                                                                  BN, cols, none);
+                                                                  BN, cols, none, 1);
     } else {
         if ((rc = opt_in_smem(gemm_kmajor_kernel<0>, kSmemKMajor))) return rc;
         gemm_kmajor_kernel<0><<<grid, kThreads, kSmemKMajor, st>>>(tmA, tmB, tmC, m_tiles, n_tiles, K,
-                                                                  BN, cols, none);
+                                                                  BN, cols, none, 1);
     }
     CME_LAUNCH_CHECK();
     return 0;
@@ -1402,9 +1445,27 @@ int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int3
     if ((rc = make_map(&tmB, W2c, (uint64_t)H, 16, (uint64_t)ldh, BK, 16))) return rc;
     if ((rc = opt_in_smem(gemm_kmajor_kernel<2>, kSmemSoftmax))) return rc;
     SoftmaxEpi sm{b2, labels, dz2, (__nv_bfloat16*)dz2b, loss_sum, pred, gb2, scale, (long long)rows, C};
+    const int nk = (H + BK - 1) / BK;
+    if (2 * m_tiles <= cme::sm_count() && nk >= 8) {
+        // few row tiles: two CTAs per tile, each streaming half of K (cluster of 2)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * m_tiles);
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmemSoftmax;
+        cfg.stream = cme::as_stream(stream);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CME_CUDA(cudaLaunchKernelEx(&cfg, gemm_kmajor_kernel<2>, tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm, 2));
+        return 0;
+    }
     const int grid = std::min(m_tiles, cme::sm_count());
     gemm_kmajor_kernel<2><<<grid, kThreads, kSmemSoftmax, cme::as_stream(stream)>>>(
-        tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm);
+        tmA, tmB, tmA, m_tiles, 1, H, 16, 32u, sm, 1);
     CME_LAUNCH_CHECK();
     return 0;
 }
