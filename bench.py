@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--reg", type=float, default=1e-4)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel separately")
+    ap.add_argument("--breakdown", action="store_true",
+                    help="also time the phases of one step separately (eager, serial, rank 0)")
     return ap.parse_args()
 
 
@@ -139,6 +141,29 @@ def run_ours(args) -> dict:
                "d2h_bytes_per_step": feeder.d2h_bytes * world // K,
                "last_loss_per_sample": float(loss_pinned[K - 1]) / in_proc}
 
+    breakdown = None
+    if args.breakdown:
+        names = ["stage", "zero_grads", "fwd1", "fwd2_softmax", "backward", "allreduce_sgd+barriers", "recast_w2"]
+        acc = {n: 0.0 for n in names}
+        reps = 5
+        for r in range(reps + 2):
+            p = r % pool
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(len(names) + 1)]
+            barrier(info)
+            ev[0].record()
+            eng.stage(x_dev[p].data_ptr(), in_proc); ev[1].record()
+            eng.grads.tensor.zero_(); ev[2].record()
+            dev.mlp_fwd1(eng.xb, eng.w1c.tensor, eng.a1, in_proc, eng.K, eng.Hh); ev[3].record()
+            eng.forward(in_proc, l_dev[p], 1.0 / (in_proc * world), skip_fwd1=True); ev[4].record()
+            eng.backward(in_proc); ev[5].record()
+            eng._reduce_range(args.lr, args.reg, (0, eng.n_total), 0); ev[6].record()
+            eng._recast_w2(); ev[7].record()
+            torch.cuda.synchronize()
+            if r >= 2:
+                for i, n in enumerate(names):
+                    acc[n] += ev[i].elapsed_time(ev[i + 1]) / reps
+        breakdown = {n: round(v, 4) for n, v in acc.items()}
+
     out = {
         "metric": "MLP train samples/s", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
@@ -156,6 +181,8 @@ def run_ours(args) -> dict:
         "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
         "tflops": value * M.flops_per_sample(H) / 1e12,
     }
+    if breakdown:
+        out["breakdown_ms"] = breakdown
     if dist.is_initialized():
         dist.destroy_process_group()
     return out if rank == 0 else {}
