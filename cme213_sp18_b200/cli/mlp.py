@@ -48,6 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--pixel-max", type=int, default=255)
     ap.add_argument("--outdir", default="Outputs")
     ap.add_argument("--device", default=None, help="cpu forces the gloo/CPU schedule")
+    ap.add_argument("--resume", default=None, help="checkpoint to start the parallel run from")
+    ap.add_argument("--save-checkpoint", default=None, help="write the trained weights here")
     return ap
 
 
@@ -95,6 +97,12 @@ def main(argv=None) -> int:
         print(f"Precision on validation set for sequential training = {prec}")
     if rank0:
         print("\nStart Parallel Training")
+    if args.resume:
+        from ..utils.checkpoint import load_checkpoint
+
+        meta = load_checkpoint(args.resume, nn)        # same file on every rank: replicas stay identical
+        if rank0:
+            print(f"Resumed from {args.resume} (epoch {meta['epoch']}, iteration {meta['iteration']})")
     precision = args.precision
     if precision == "auto":
         precision = "fp64" if (args.grade or args.debug) else "bf16"
@@ -115,6 +123,10 @@ def main(argv=None) -> int:
         prec = M.precision(M.predict(nn, x_dev), l_dev)
         print(f"Precision on validation set for parallel training = {prec}")
         grading.save_label(out / "Pred_testset.txt", M.predict(nn, x_test))
+        if args.save_checkpoint:
+            from ..utils.checkpoint import save_checkpoint
+
+            save_checkpoint(args.save_checkpoint, nn, epoch=args.epochs)
     rc = 0
     if (args.grade or args.debug) and rank0:
         if dl:

@@ -84,6 +84,11 @@ def sigmoid(z: torch.Tensor) -> torch.Tensor:
     return 1.0 / (1.0 + torch.exp(-z))
 
 
+def relu(z: torch.Tensor) -> torch.Tensor:
+    """ref fpcode/utils/common.cpp:73-76 (defined there, never used by the trainer)."""
+    return torch.clamp_min(z, 0.0)
+
+
 def softmax(z: torch.Tensor) -> torch.Tensor:
     """Row-wise softmax with the max subtracted (the reference does not subtract it, ref
     fpcode/utils/common.cpp:13-18; identical in exact arithmetic)."""

@@ -109,3 +109,25 @@ def test_letter_histogram():
     assert h[ord("a")] == 4 and h[ord("z")] == 1 and h.sum() == 9
     h2 = host.letter_histogram(t, stride=3, offset=1)
     assert h2[ord("b")] == 2 and h2[ord("a")] == 1 and h2.sum() == 3
+
+
+def test_ulp_helpers_and_strided_range():
+    from cme213_sp18_b200.utils import strided, ulp
+
+    assert ulp.almost_equal_ulps(1.0, np.nextafter(1.0, 2.0), max_ulps=1)
+    assert not ulp.almost_equal_ulps(1.0, 1.0 + 1e-9, max_ulps=512)
+    m = np.arange(6, dtype=np.float64).reshape(2, 3)
+    assert ulp.almost_equal_matrix(m, m.T.ravel(), column_major=True)
+    assert ulp.almost_equal_matrix(m, m.ravel(), column_major=False)
+    assert not ulp.almost_equal_matrix(m, m.ravel(), column_major=True)
+    assert ulp.max_ulps_f32([1.0, 2.0], [1.0, np.nextafter(np.float32(2.0), np.float32(3.0))]) == 1
+    assert list(strided.strided_range(list(range(10)), 1, 3)) == [1, 4, 7]
+    assert strided.strided_range(np.arange(10), 2, 4, 9).tolist() == [2, 6]
+
+
+def test_vector_file_roundtrip(tmp_path):
+    from cme213_sp18_b200.utils import vecio
+
+    v = np.array([3, 0, 4294967295, 17], dtype=np.uint32)
+    vecio.write_vector_to_file(tmp_path / "vec", v)
+    assert np.array_equal(vecio.read_vector_from_file(tmp_path / "vec"), v)

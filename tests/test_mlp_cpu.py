@@ -161,3 +161,17 @@ shutdown()
                          capture_output=True, text=True, env=env, timeout=170)
     assert res.returncode == 0, res.stdout + res.stderr
     assert "GLOO_OK" in res.stdout
+
+
+def test_relu_and_cli_checkpoint_resume(tmp_path):
+    assert torch.equal(M.relu(torch.tensor([-1.0, 0.0, 2.0])), torch.tensor([0.0, 0.0, 2.0]))
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2")
+    base = [sys.executable, "-m", "cme213_sp18_b200.cli.mlp", "--device", "cpu", "-n", "16", "-e", "1", "-b", "200",
+            "-l", "0.1", "--train-size", "1000", "--test-size", "20", "--pixel-max", "1",
+            "--data-dir", str(tmp_path / "none"), "--outdir", str(tmp_path / "Outputs")]
+    r1 = subprocess.run(base + ["--save-checkpoint", str(tmp_path / "ck.pt")], capture_output=True, text=True,
+                        cwd=tmp_path, env=env, timeout=200)
+    assert r1.returncode == 0 and (tmp_path / "ck.pt").exists(), r1.stdout + r1.stderr
+    r2 = subprocess.run(base + ["--resume", str(tmp_path / "ck.pt")], capture_output=True, text=True, cwd=tmp_path,
+                        env=env, timeout=200)
+    assert r2.returncode == 0 and "Resumed from" in r2.stdout, r2.stdout + r2.stderr
