@@ -164,3 +164,29 @@ shutdown()
     res = _torchrun(script, 2, 29541)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "TWO_GPU_OK" in res.stdout
+
+
+def test_streaming_feeder_matches_resident_training():
+    """The end-to-end path (pinned host -> device every step, loss read back every step) must
+    train exactly like the device-resident path, including under CUDA-graph replay."""
+    from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+    from cme213_sp18_b200.parallel.dp_trainer import StreamingFeeder
+
+    H, bs, steps = [784, 128, 10], 500, 6
+    x, lab = mnist.synthetic_mnist(bs * 3, seed=11, pixel_max=1)
+    nn = M.NeuralNetwork(H)
+    a, b = MLPEngineBF16(H, bs, _info()), MLPEngineBF16(H, bs, _info())
+    a.load_params(nn)
+    b.load_params(nn)
+    xd, ld = x.cuda(), lab.cuda()
+    batches = [((i % 3) * bs, bs) for i in range(steps)]
+    for start, n in batches:
+        a.step(xd[start:start + n].data_ptr(), ld[start:start + n], n, 0.5, 1e-4, n)
+    feeder = StreamingFeeder(b, 784, graph=True)
+    losses = torch.zeros(steps, dtype=torch.float32).pin_memory()
+    feeder.run(x.pin_memory(), lab.pin_memory(), batches, 0.5, 1e-4, 1, 0, losses)
+    torch.cuda.synchronize()
+    d = (a.params.tensor - b.params.tensor).abs().max() / a.params.tensor.abs().max()
+    assert float(d) < 1e-4, float(d)
+    assert feeder.h2d_bytes == steps * bs * (784 + 4) and feeder.d2h_bytes == 4 * steps
+    assert float(losses[0]) > float(losses[-1]) > 0
