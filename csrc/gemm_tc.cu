@@ -360,9 +360,11 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 // 256-row B tile, the leader issues tcgen05.mma.cta_group::2 with M = 256, and the hardware
 // reads the two halves of B from both CTAs' shared memory.  Each CTA keeps its 128 x 256
 // accumulator in its own TMEM and runs its own epilogue.
-constexpr int kStages2 = 6;
+constexpr int kStages2 = 6;                  // MN-major pair kernel: no output staging
+constexpr int kStagesK2 = 5;                 // K-major pair kernel: one stage less, four staging buffers
+constexpr int kThreadsK2 = 320;              // producer warp + MMA warp + 8 epilogue warps
 constexpr int kB2Bytes = 128 * BK * 2;       // this CTA's half of the B tile: 16 KB
-constexpr int kSmemKMajor2 = kStages2 * (kABytes + kB2Bytes) + 2 * kStageBytes + 1024 + 256;
+constexpr int kSmemKMajor2 = kStagesK2 * (kABytes + kB2Bytes) + 4 * kStageBytes + 1024 + 256;
 constexpr int kSmemMNMajor2 = kStages2 * (kABytes + kB2Bytes) + 1024 + 256;
 
 struct Barriers2 {
@@ -373,16 +375,21 @@ struct Barriers2 {
     uint32_t tmem_base;
 };
 
+// The epilogue (TMEM -> sigmoid -> bf16 -> swizzled smem -> TMA store of 128 x 256 outputs per
+// CTA and tile) was the limiter with four warps (ncu: tensor pipe 65 % busy).  Eight epilogue
+// warps work as two groups, each owning two of the four 64-column chunks with its own pair of
+// staging buffers, named barrier and TMA-store leader; the sigmoid is evaluated two at a time
+// (tanh.approx.bf16x2).
 template <int EPI /* 0 = identity, 1 = sigmoid */>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsK2, 1)
 gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, int m_tiles, int n_tiles, int K) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
-    uint8_t* sB = sA + kStages2 * kABytes;
-    uint8_t* sC = sB + kStages2 * kB2Bytes;
-    Barriers2* bars = (Barriers2*)(sC + 2 * kStageBytes);
+    uint8_t* sB = sA + kStagesK2 * kABytes;
+    uint8_t* sC = sB + kStagesK2 * kB2Bytes;
+    Barriers2* bars = (Barriers2*)(sC + 4 * kStageBytes);
     constexpr int BN = 256;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -393,13 +400,13 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         prefetch_tmap(&tmA);
         prefetch_tmap(&tmB);
         prefetch_tmap(&tmC);
-        for (int s = 0; s < kStages2; ++s) {
+        for (int s = 0; s < kStagesK2; ++s) {
             mbar_init(&bars->full[s], 1);
             mbar_init(&bars->empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&bars->tmem_full[a], 1);
-            mbar_init(&bars->tmem_empty[a], 8);
+            mbar_init(&bars->tmem_empty[a], 16);   // 8 epilogue warps x 2 CTAs
         }
         fence_barrier_init();
     }
@@ -427,7 +434,7 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     if (cta == 0) mbar_expect_tx(&bars->full[stage], 2 * (kABytes + kB2Bytes));
                     tma_load_2d_2cta(sA + stage * kABytes, &tmA, &bars->full[stage], kb * BK, m0);
                     tma_load_2d_2cta(sB + stage * kB2Bytes, &tmB, &bars->full[stage], kb * BK, n0);
-                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                    if (++stage == kStagesK2) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -452,7 +459,7 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         umma_bf16_2cta(d_tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc,
                                        (kb | j) != 0);
                     umma_commit_2cta(&bars->empty[stage]);
-                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                    if (++stage == kStagesK2) { stage = 0; phase ^= 1; }
                 }
                 umma_commit_2cta(&bars->tmem_full[acc]);
                 acc ^= 1;
@@ -461,9 +468,11 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         __syncwarp();
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3;                          // TMEM sub-partition of this warp
+        const int grp = (warp - 2) >> 2;                 // 0: chunks 0,1   1: chunks 2,3
         const int row = q * 32 + lane;
-        const bool leader = (warp == 2 && lane == 0);
+        const bool leader = (((warp - 2) & 3) == 0 && lane == 0);
+        uint8_t* my_stage = sC + grp * 2 * kStageBytes;
         int acc = 0;
         uint32_t acc_phase = 0;
         int cbuf = 0;
@@ -473,24 +482,27 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-            for (int c = 0; c < BN / 64; ++c) {
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+                const int c = grp * 2 + cc;
                 if (leader) tma_store_wait_read<1>();
-                named_bar_sync(1, 128);
-                uint8_t* stg = sC + cbuf * kStageBytes;
+                named_bar_sync(1 + grp, 128);
+                uint8_t* stg = my_stage + cbuf * kStageBytes;
+                uint32_t v0[32], v1[32];
+                tmem_ld_32x32(t_row + (uint32_t)(c * 64), v0);
+                tmem_ld_32x32(t_row + (uint32_t)(c * 64 + 32), v1);
+                tmem_ld_wait();
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_row + (uint32_t)(c * 64 + half * 32), v);
-                    tmem_ld_wait();
+                    const uint32_t* v = half ? v1 : v0;
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         uint32_t p[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            float x0 = __uint_as_float(v[g * 8 + 2 * e]);
-                            float x1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
-                            if (EPI == 1) { x0 = sigmoid_fast(x0); x1 = sigmoid_fast(x1); }
-                            p[e] = pack_bf16(x0, x1);
+                            const float x0 = __uint_as_float(v[g * 8 + 2 * e]);
+                            const float x1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                            p[e] = (EPI == 1) ? sigmoid2_bf16(x0, x1) : pack_bf16(x0, x1);
                         }
                         const int chunk = half * 4 + g;
                         const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
@@ -498,7 +510,7 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                 }
                 fence_proxy_async_smem();
-                named_bar_sync(1, 128);
+                named_bar_sync(1 + grp, 128);
                 if (leader) {
                     tma_store_2d(&tmC, stg, n0 + c * 64, m0);
                     tma_store_commit();
@@ -668,13 +680,16 @@ gemm_mnmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_mnmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      float* __restrict__ G, int ldg, int M, int N, int m_tiles, int n_tiles,
-                     int kb_total, int ksplit) {
+                     int kb_total, int ksplit, int BN) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sA = smem;
     uint8_t* sB = sA + kStages2 * kABytes;
     Barriers2* bars = (Barriers2*)(sB + kStages2 * kB2Bytes);
-    constexpr int BN = 256;
+    // BN (a multiple of 16, <= 256) is the width of the pair's tile; each CTA stages BN/2 of
+    // the columns (one or two 64-wide boxes) and keeps its accumulators 256 TMEM columns apart
+    const int half_n = BN / 2;
+    const int nb_boxes = (half_n + 63) / 64;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cta = cluster_ctarank();
@@ -714,16 +729,17 @@ gemm_mnmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 const int kb0 = (int)((long long)kb_total * kc / ksplit);
                 const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
                 const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
-                const int n0 = (tile % n_tiles) * BN + (int)cta * 128;
+                const int n0 = (tile % n_tiles) * BN + (int)cta * half_n;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
-                    if (cta == 0) mbar_expect_tx(&bars->full[stage], 2 * (kABytes + kB2Bytes));
+                    if (cta == 0)
+                        mbar_expect_tx(&bars->full[stage], 2 * (kABytes + (uint32_t)nb_boxes * 8192u));
                     uint8_t* a = sA + stage * kABytes;
                     uint8_t* b = sB + stage * kB2Bytes;
                     tma_load_2d_2cta(a, &tmA, &bars->full[stage], m0, kb * BK);
                     tma_load_2d_2cta(a + 8192, &tmA, &bars->full[stage], m0 + 64, kb * BK);
-                    tma_load_2d_2cta(b, &tmB, &bars->full[stage], n0, kb * BK);
-                    tma_load_2d_2cta(b + 8192, &tmB, &bars->full[stage], n0 + 64, kb * BK);
+                    for (int x = 0; x < nb_boxes; ++x)
+                        tma_load_2d_2cta(b + x * 8192, &tmB, &bars->full[stage], n0 + x * 64, kb * BK);
                     if (++stage == kStages2) { stage = 0; phase ^= 1; }
                 }
             }
@@ -740,7 +756,7 @@ gemm_mnmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 const int kb1 = (int)((long long)kb_total * (kc + 1) / ksplit);
                 mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&bars->full[stage], phase);
                     tc_fence_after();
@@ -771,7 +787,7 @@ gemm_mnmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             const int n0 = (tile % n_tiles) * BN;
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
-            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256);
             const int h = m0 + q * 32 + lane;
             float* grow = G + (size_t)h * ldg;
             for (int c = 0; c < BN / 16; ++c) {
@@ -1345,10 +1361,10 @@ int launch_kmajor(int epi, const void* A, const void* B, void* Cout, int64_t M, 
         int pairs = (int)std::min<long long>(t2, cme::sm_count() / 2);
         if (epi == 1) {
             if ((rc = opt_in_smem(gemm_kmajor2_kernel<1>, kSmemKMajor2))) return rc;
-            gemm_kmajor2_kernel<1><<<2 * pairs, kThreads, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
+            gemm_kmajor2_kernel<1><<<2 * pairs, kThreadsK2, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
         } else {
             if ((rc = opt_in_smem(gemm_kmajor2_kernel<0>, kSmemKMajor2))) return rc;
-            gemm_kmajor2_kernel<0><<<2 * pairs, kThreads, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
+            gemm_kmajor2_kernel<0><<<2 * pairs, kThreadsK2, kSmemKMajor2, st>>>(tmA, tmB2, tmC, m2, n2, K);
         }
         CME_LAUNCH_CHECK();
         return 0;
@@ -1408,14 +1424,18 @@ int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K,
     // CTA-pair path for big problems: 256 x 256 tiles (columns past K are masked in the epilogue)
     static const bool pairs_off = getenv("CME_NO_PAIRS") != nullptr;
     if (!pairs_off && H >= 512 && K >= 256 && kb_total >= 16) {
+        // 256-wide column tiles.  Narrower equal-width tiles (785 columns -> 4 x 208, 5.6 % padding
+        // instead of 23 %) were measured SLOWER (0.71 vs 0.62 ms): with cta_group::2 the MMA time
+        // does not shrink with N = 208 and each CTA's 104 columns leave a partial swizzle group.
         const int m2 = (H + 255) / 256, n2 = (K + 255) / 256;
+        const int BN2 = 256;
         const int npairs = cme::sm_count() / 2;
         const int ks = choose_ksplit(m2 * n2, kb_total, npairs);
         if ((rc = opt_in_smem(gemm_mnmajor2_kernel, kSmemMNMajor2))) return rc;
         const long long items2 = (long long)m2 * n2 * ks;
         const int pairs = (int)std::min<long long>(items2, npairs);
         gemm_mnmajor2_kernel<<<2 * pairs, kThreads, kSmemMNMajor2, cme::as_stream(stream)>>>(
-            tmA, tmB, gW1, ldg, H, K, m2, n2, kb_total, ks);
+            tmA, tmB, gW1, ldg, H, K, m2, n2, kb_total, ks, BN2);
         CME_LAUNCH_CHECK();
         return 0;
     }

@@ -284,6 +284,15 @@ __device__ __forceinline__ float tanh_approx(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// two sigmoids per MUFU op: inputs rounded to bf16, tanh.approx.bf16x2, result packed bf16x2
+// (lo = sigmoid(x0), hi = sigmoid(x1)); the output is stored as bf16 anyway
+__device__ __forceinline__ uint32_t sigmoid2_bf16(float x0, float x1) {
+    uint32_t h, t, r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(0.5f * x1), "f"(0.5f * x0));
+    asm("tanh.approx.bf16x2 %0, %1;" : "=r"(t) : "r"(h));
+    asm("fma.rn.bf16x2 %0, %1, %2, %2;" : "=r"(r) : "r"(t), "r"(0x3F003F00u));   // 0.5 * t + 0.5
+    return r;
+}
 __device__ __forceinline__ float sigmoid_fast(float x) {
     return fmaf(tanh_approx(0.5f * x), 0.5f, 0.5f);
 }
