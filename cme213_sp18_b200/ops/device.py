@@ -416,3 +416,96 @@ def mlp_step_native(plan, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: fl
     check(lib.cme_mlp_step(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
                            stream_ptr()), "cme_mlp_step")
     _count(9 if plan.nranks == 1 else 11)
+
+
+def warmup() -> int:
+    """Context + module warm-up with one trivial kernel (ref fpcode/gpu_func.cu:11-36 device_add_one);
+    returns 1 when the kernel ran."""
+    import ctypes as C
+
+    lib = device_lib()
+    lib.cme_warmup.argtypes = [C.POINTER(C.c_int)]
+    lib.cme_warmup.restype = C.c_int
+    v = C.c_int(0)
+    check(lib.cme_warmup(C.byref(v)), "cme_warmup")
+    _count(1)
+    return v.value
+
+
+class MlpRuntime:
+    """Handle on the native streaming trainer (csrc/mlp_runtime.cu, cme_mlp_runtime_*): the whole
+    minibatch loop of parallel_train (ref fpcode/neural_network.cpp:443-567) runs in C++, fed
+    from pinned host memory, with one CUDA graph per step."""
+
+    def __init__(self, engine, graphs: bool = True):
+        import ctypes as C
+
+        lib = device_lib()
+        lib.cme_mlp_runtime_create.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        lib.cme_mlp_runtime_create.restype = C.c_int
+        lib.cme_mlp_runtime_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        lib.cme_mlp_runtime_run.restype = C.c_int
+        lib.cme_mlp_runtime_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        lib.cme_mlp_runtime_stats.restype = C.c_int
+        lib.cme_mlp_runtime_destroy.argtypes = [C.c_void_p]
+        lib.cme_mlp_runtime_destroy.restype = C.c_int
+        self._lib = lib
+        self.engine = engine               # keeps the buffers named by the plan alive
+        self.plan = make_mlp_plan(engine)
+        h = C.c_void_p()
+        with torch.cuda.device(engine.info.device):
+            check(lib.cme_mlp_runtime_create(C.addressof(self.plan), int(graphs), C.byref(h)),
+                  "cme_mlp_runtime_create")
+        self._h = h
+        self._counted = 0
+
+    def run(self, x_host: torch.Tensor, lab_host: torch.Tensor, row_begin, rows, global_rows,
+            lr: float, reg: float, loss_host: torch.Tensor | None = None) -> int:
+        """x_host [N, D] uint8 and lab_host [N] int32 must be pinned; row_begin / rows /
+        global_rows are per-step sequences (this rank's first row, its row count, the global
+        sample count of the minibatch).  Asynchronous: synchronise the current stream (or read
+        an event) before touching loss_host."""
+        import ctypes as C
+
+        n = len(rows)
+        if not (x_host.is_pinned() and lab_host.is_pinned()):
+            raise ValueError("MlpRuntime.run needs pinned host tensors")
+        if x_host.dtype != torch.uint8 or lab_host.dtype != torch.int32 or not x_host.is_contiguous():
+            raise ValueError("MlpRuntime.run needs contiguous uint8 pixels and int32 labels")
+        if x_host.shape[1] != self.plan.D:
+            raise ValueError(f"rows have {x_host.shape[1]} features, the plan expects {self.plan.D}")
+        hi = max((b + r for b, r in zip(row_begin, rows)), default=0)
+        if hi > x_host.shape[0] or hi > lab_host.shape[0]:
+            raise ValueError("a step reads past the end of the host arrays")
+        if loss_host is not None and (not loss_host.is_pinned() or loss_host.numel() < n
+                                      or loss_host.dtype != torch.float32):
+            raise ValueError("loss_host must be pinned float32 with one element per step")
+        arr = C.c_int64 * n
+        rb, rr, gr = arr(*row_begin), arr(*rows), arr(*global_rows)
+        with torch.cuda.device(self.engine.info.device):
+            check(self._lib.cme_mlp_runtime_run(self._h, x_host.data_ptr(), lab_host.data_ptr(), rb, rr, gr, n,
+                                                lr, reg, loss_host.data_ptr() if loss_host is not None else None,
+                                                stream_ptr()), "cme_mlp_runtime_run")
+        st = self.stats()
+        _count(st["launches"] - self._counted)
+        self._counted = st["launches"]
+        return n
+
+    def stats(self) -> dict:
+        import ctypes as C
+
+        out = (C.c_int64 * 5)()
+        check(self._lib.cme_mlp_runtime_stats(self._h, out), "cme_mlp_runtime_stats")
+        return dict(zip(("h2d_bytes", "d2h_bytes", "launches", "steps", "graphs"), [int(v) for v in out]))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.cme_mlp_runtime_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass

@@ -195,13 +195,23 @@ def parallel_train(nn, X, labels, learning_rate: float = 0.001, reg: float = 0.0
                    comm: str = "fused", data_mode: str = "owner", debug_log=None, log=print) -> dict:
     """Same call shape as the reference's parallel_train (ref fpcode/inc/neural_network.h:44-47).
     X: [N, D] uint8 (or float) images, labels: [N] class ids; only rank 0 needs them in "owner"
-    mode.  On return `nn` holds the trained weights on every rank."""
+    mode.  data_mode="stream" keeps the dataset in pinned host memory and feeds every step
+    through the native runtime (stream_train).  On return `nn` holds the trained weights on
+    every rank."""
     del grad_check  # the analytic/numeric check lives in the serial trainer and the tests
     info = info or DistInfo(device=torch.device("cuda" if torch.cuda.is_available() else "cpu"))
     if info.device.type == "cpu":
         return parallel_train_cpu(nn, X, labels, learning_rate, reg, epochs, batch_size, info,
                                   debug_log=debug_log if debug else None, print_every=print_every)
     t0 = time.perf_counter()
+    if data_mode == "stream":
+        if precision != "bf16" or X is None:
+            raise ValueError('data_mode="stream" is the bf16 engine fed from host memory: every rank passes X')
+        Xs = X if X.dtype == torch.uint8 else X.round().clamp(0, 255).to(torch.uint8)
+        out = stream_train(nn, Xs, labels, learning_rate, reg, epochs, batch_size, info, comm=comm,
+                           print_every=print_every, log=log)
+        out["seconds"] = time.perf_counter() - t0
+        return out
     trainer = DataParallelTrainer(nn.H, batch_size, info, precision=precision, comm=comm,
                                   data_mode=data_mode)
     Xu8 = None
@@ -272,3 +282,80 @@ class StreamingFeeder:
             loss_out[i: i + 1].copy_(eng.loss, non_blocking=True)
             self.d2h_bytes += 4
         return len(batches)
+
+
+class NativeFeeder:
+    """Same job as StreamingFeeder with the loop in C++ (csrc/mlp_runtime.cu): one call queues
+    every step of the run (H2D on a copy stream, one CUDA graph per step, loss read-back), so
+    the Python interpreter is not on the per-step path at all.  The step inside is
+    cme_mlp_step, i.e. the single-stream schedule without the bucketed overlap of
+    MLPEngineBF16; prefer StreamingFeeder when several ranks train a wide layer."""
+
+    def __init__(self, engine, D: int, graph: bool = True):
+        from ..ops import device as dev
+
+        if D != engine.D:
+            raise ValueError(f"feeder built for {D} features, the engine has {engine.D}")
+        self.eng = engine
+        self.rt = dev.MlpRuntime(engine, graphs=graph)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run(self, x_host: torch.Tensor, lab_host: torch.Tensor, batches, lr: float, reg: float,
+            world: int, rank: int, loss_out: torch.Tensor | None) -> int:
+        """batches: list of (start, in_proc) as for StreamingFeeder.run."""
+        batches = [b for b in batches if b[1] > 0]
+        if not batches:
+            return 0
+        before = self.rt.stats()
+        begin = [start + rank * in_proc for start, in_proc in batches]
+        rows = [in_proc for _, in_proc in batches]
+        glob = [in_proc * world for _, in_proc in batches]
+        n = self.rt.run(x_host, lab_host, begin, rows, glob, lr, reg, loss_out)
+        after = self.rt.stats()
+        self.h2d_bytes += after["h2d_bytes"] - before["h2d_bytes"]
+        self.d2h_bytes += after["d2h_bytes"] - before["d2h_bytes"]
+        return n
+
+
+def stream_train(nn, X_u8: torch.Tensor, labels: torch.Tensor, learning_rate: float, reg: float,
+                 epochs: int, batch_size: int, info: DistInfo, comm: str = "fused", native: bool = True,
+                 print_every: int = -1, log=print) -> dict:
+    """parallel_train for a dataset that stays in host memory: every rank holds (or maps) the
+    full uint8 dataset in pinned memory and streams its slice of each minibatch to the device
+    (ref fpcode/neural_network.cpp:443-567 does this with blocking copies and host scatters).
+    Returns {'iterations', 'losses'} like the resident trainer; losses are the per-sample
+    cross-entropy of this rank's slice at the print_every iterations."""
+    from ..models.mlp_engine import MLPEngineBF16
+
+    world, rank = info.world, info.rank
+    N, D = X_u8.shape
+    eng = MLPEngineBF16(nn.H, max(1, batch_size // world), info, comm=comm)
+    eng.load_params(nn)
+    xp = X_u8 if X_u8.is_pinned() else X_u8.contiguous().pin_memory()
+    lab32 = labels.to(torch.int32)
+    lp = lab32 if lab32.is_pinned() else lab32.contiguous().pin_memory()
+    feeder = (NativeFeeder if native else StreamingFeeder)(eng, D)
+    num_batches = (N + batch_size - 1) // batch_size
+    batches = []
+    for _ in range(epochs):
+        for b in range(num_batches):
+            start = b * batch_size
+            batches.append((start, M.dp_in_proc(batch_size, N - start, world)))
+    live = [b for b in batches if b[1] > 0]
+    loss_host = torch.zeros(max(1, len(live)), dtype=torch.float32).pin_memory()
+    feeder.run(xp, lp, live, learning_rate, reg, world, rank, loss_host)
+    torch.cuda.synchronize()
+    losses = []
+    if print_every > 0:
+        k = 0
+        for it, (start, in_proc) in enumerate(batches):
+            if in_proc <= 0:
+                continue
+            if it % print_every == 0:
+                losses.append((it, float(loss_host[k]) / in_proc))
+                if info.is_main:
+                    log(f"Loss at iteration {it} = {losses[-1][1]}")
+            k += 1
+    eng.store_params(nn)
+    return {"iterations": len(batches), "losses": losses, "h2d_bytes": feeder.h2d_bytes}

@@ -30,7 +30,26 @@ int sm_count() {
 
 }  // namespace cme
 
+namespace {
+__global__ void add_one_kernel(int* v) { *v += 1; }
+}  // namespace
+
 extern "C" {
+
+int cme_warmup(int* value_inout) {
+    CME_CHECK_ARG(value_inout, "cme_warmup: null argument");
+    int* d = nullptr;
+    CME_CUDA(cudaMalloc(&d, sizeof(int)));
+    cudaError_t e = cudaMemcpy(d, value_inout, sizeof(int), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        add_one_kernel<<<1, 1>>>(d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(value_inout, d, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    CME_CUDA(e);
+    return 0;
+}
 
 const char* cme_last_error(void) { return cme::g_err; }
 

@@ -24,6 +24,9 @@ const char* cme_last_error(void);
 int cme_version(void);
 /* sm_count / cc_major / cc_minor of the current device (any may be NULL). */
 int cme_device_info(int* sm_count, int* cc_major, int* cc_minor);
+/* Creates the context, loads the module and runs one trivial kernel, then waits for it
+ * (the reference's device_add_one warm-up, ref fpcode/gpu_func.cu:11-36). *value_inout += 1. */
+int cme_warmup(int* value_inout);
 
 /* ---- hw2 q1: byte shift (ref hw2code/shift.cu:13-99) -----------------------
  * out[i] = in[i] + shift (mod 256) for i < n.  variant: 0 = one byte per thread
@@ -283,6 +286,27 @@ typedef struct CmeMlpPlan {
  * (ref fpcode/neural_network.cpp:484-541). */
 int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
                  float lr, float reg, float scale, float* loss_sum, void* stream);
+
+/* Native streaming trainer (csrc/mlp_runtime.cu): the C++ counterpart of parallel_train's
+ * whole minibatch loop (ref fpcode/neural_network.cpp:443-567) for data that lives in pinned
+ * host memory.  create() allocates two device staging slots (max_rows x D uint8 + max_rows
+ * int32 each), two streams and the events; it copies *plan (the buffers it names must outlive
+ * the runtime).  run() issues `nsteps` steps without waiting for the device: step i trains on
+ * rows [row_begin[i], row_begin[i] + rows[i]) of host_x [.][D] / host_labels (this rank's
+ * slice, pinned), with gradient scale 1 / global_rows[i]; the H2D copy of step i+1 overlaps
+ * step i; each step is replayed from a CUDA graph (use_graphs) recorded on first use; the
+ * summed cross-entropy of step i is stored by the device into loss_host[i] (pinned and
+ * device-mapped, i.e. cudaHostAlloc / cudaHostRegister memory; may be NULL).  Work is ordered
+ * after everything already queued on `stream`, and `stream` waits for the last step; the host
+ * arrays must stay valid until then.  With several ranks every rank runs the same steps. */
+typedef struct CmeMlpRuntime CmeMlpRuntime;
+int cme_mlp_runtime_create(const CmeMlpPlan* plan, int use_graphs, CmeMlpRuntime** out);
+int cme_mlp_runtime_run(CmeMlpRuntime* rt, const uint8_t* host_x, const int32_t* host_labels,
+                        const int64_t* row_begin, const int64_t* rows, const int64_t* global_rows,
+                        int nsteps, float lr, float reg, float* loss_host, void* stream);
+/* out = {h2d bytes, d2h bytes, kernels launched, steps, graphs recorded} since create(). */
+int cme_mlp_runtime_stats(const CmeMlpRuntime* rt, int64_t out[5]);
+int cme_mlp_runtime_destroy(CmeMlpRuntime* rt);
 
 /* Cross-GPU flag barrier over a peer-mapped pad of uint32 slots.  pads: DEVICE
  * array of nranks pointers (one pad per rank, >= 8*64 slots, zero-initialised).

@@ -190,3 +190,58 @@ def test_streaming_feeder_matches_resident_training():
     assert float(d) < 1e-4, float(d)
     assert feeder.h2d_bytes == steps * bs * (784 + 4) and feeder.d2h_bytes == 4 * steps
     assert float(losses[0]) > float(losses[-1]) > 0
+
+
+@pytest.mark.parametrize("graphs", [True, False])
+def test_native_runtime_matches_streaming_feeder(graphs):
+    """cme_mlp_runtime_run (the C++ minibatch loop: copy stream, graph per step, loss read-back)
+    against the Python-driven feeder, with a short last batch."""
+    from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+    from cme213_sp18_b200.parallel.dp_trainer import NativeFeeder, StreamingFeeder
+
+    H, bs = [784, 128, 10], 500
+    x, lab = mnist.synthetic_mnist(bs * 3 - 100, seed=12, pixel_max=1)
+    nn = M.NeuralNetwork(H)
+    a, b = MLPEngineBF16(H, bs, _info()), MLPEngineBF16(H, bs, _info())
+    a.load_params(nn)
+    b.load_params(nn)
+    batches = [(0, bs), (bs, bs), (2 * bs, bs - 100)] * 2
+    xp, lp = x.pin_memory(), lab.pin_memory()
+    la = torch.zeros(len(batches), dtype=torch.float32).pin_memory()
+    lb = torch.zeros(len(batches), dtype=torch.float32).pin_memory()
+    StreamingFeeder(a, 784, graph=graphs).run(xp, lp, batches, 0.5, 1e-4, 1, 0, la)
+    nf = NativeFeeder(b, 784, graph=graphs)
+    nf.run(xp, lp, batches, 0.5, 1e-4, 1, 0, lb)
+    torch.cuda.synchronize()
+    d = (a.params.tensor - b.params.tensor).abs().max() / a.params.tensor.abs().max()
+    assert float(d) < 1e-4, float(d)
+    assert torch.allclose(la, lb, rtol=1e-3), (la, lb)
+    rows = sum(n for _, n in batches)
+    assert nf.h2d_bytes == rows * (784 + 4) and nf.d2h_bytes == 4 * len(batches)
+    st = nf.rt.stats()
+    assert st["steps"] == len(batches) and st["graphs"] == (4 if graphs else 0)
+    # a second run on the same runtime reuses the recorded graphs
+    nf.run(xp, lp, batches[:3], 0.5, 1e-4, 1, 0, lb)
+    torch.cuda.synchronize()
+    assert nf.rt.stats()["graphs"] == (4 if graphs else 0)
+    nf.rt.close()
+
+
+def test_stream_mode_of_parallel_train_learns():
+    from cme213_sp18_b200.parallel.dist import DistInfo
+    from cme213_sp18_b200.parallel.dp_trainer import parallel_train
+
+    x, lab = mnist.synthetic_mnist(4000, seed=3, pixel_max=1)
+    nn = M.NeuralNetwork([784, 64, 10])
+    out = parallel_train(nn, x, lab, learning_rate=0.5, reg=1e-4, epochs=6, batch_size=500,
+                         info=DistInfo(device=torch.device("cuda", 0)), data_mode="stream", print_every=8,
+                         log=lambda *_: None)
+    assert out["iterations"] == 48 and out["losses"][0][1] > out["losses"][-1][1]
+    acc = M.precision(M.predict(nn, x.double()), lab)
+    assert acc > 0.9, acc
+
+
+def test_warmup_kernel_runs():
+    from cme213_sp18_b200.ops import device as dev
+
+    assert dev.warmup() == 1
