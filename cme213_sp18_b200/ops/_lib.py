@@ -88,8 +88,11 @@ _HOST_SIGS = {
     "cmeh_max_ulp_f32": [P, P, c_size_t, P],
     "cmeh_max_ulp_f64": [P, P, c_size_t, P],
     "cmeh_letter_histogram": [P, c_size_t, c_size_t, c_size_t, P],
+    "cmeh_idx_info": [C.c_char_p, P, P],
+    "cmeh_idx_read": [C.c_char_p, c_i64, c_i64, P],
 }
-_HOST_RESTYPES = {"cmeh_max_ulp_f32": c_i64, "cmeh_max_ulp_f64": c_i64}
+_HOST_RESTYPES = {"cmeh_max_ulp_f32": c_i64, "cmeh_max_ulp_f64": c_i64, "cmeh_idx_info": c_i64,
+                  "cmeh_idx_read": c_i64}
 
 
 def _declare(lib, sigs, restypes, strict):

@@ -182,3 +182,22 @@ def letter_histogram(text: np.ndarray, stride: int = 1, offset: int = 0) -> np.n
     out = np.zeros(256, dtype=np.uint64)
     host_lib().cmeh_letter_histogram(np_ptr(t), t.size, stride, offset, np_ptr(out))
     return out
+
+
+# ---------------------------------------------------------------- fpcode: IDX files
+def idx_info(path) -> tuple[int, tuple[int, int, int]]:
+    """(magic, (count, rows, cols)) of an IDX file (ref fpcode/utils/mnist.cpp:9-35)."""
+    magic = C.c_int32(0)
+    dims = (C.c_int64 * 3)()
+    off = host_lib().cmeh_idx_info(str(path).encode(), C.addressof(magic), dims)
+    if off < 0:
+        raise ValueError(f"{path}: not a readable IDX file (code {off})")
+    return int(magic.value), (int(dims[0]), int(dims[1]), int(dims[2]))
+
+
+def idx_read(path, first_item: int, num_items: int, item_bytes: int) -> np.ndarray:
+    out = np.empty(num_items * item_bytes, dtype=np.uint8)
+    got = host_lib().cmeh_idx_read(str(path).encode(), first_item, num_items, np_ptr(out))
+    if got != out.size:
+        raise ValueError(f"{path}: short or bad IDX read (code {got})")
+    return out

@@ -21,26 +21,28 @@ NUM_TEST = 10000
 
 
 def read_idx_images(path, max_images: int | None = None) -> torch.Tensor:
-    """[N, rows*cols] uint8. Header is big-endian (ref mnist.cpp reverse_int :9-18)."""
-    raw = Path(path).read_bytes()
-    magic, n, rows, cols = struct.unpack(">IIII", raw[:16])
+    """[N, rows*cols] uint8, read by the native host library. Header is big-endian (ref
+    mnist.cpp reverse_int :9-18)."""
+    from ..ops import host
+
+    magic, (n, rows, cols) = host.idx_info(path)
     if magic != 2051:
         raise ValueError(f"{path}: bad IDX image magic {magic}")
     if max_images is not None:
         n = min(n, max_images)
-    a = np.frombuffer(raw, dtype=np.uint8, count=n * rows * cols, offset=16)
-    return torch.from_numpy(a.reshape(n, rows * cols).copy())
+    a = host.idx_read(path, 0, n, rows * cols)
+    return torch.from_numpy(a.reshape(n, rows * cols))
 
 
 def read_idx_labels(path, max_labels: int | None = None) -> torch.Tensor:
-    raw = Path(path).read_bytes()
-    magic, n = struct.unpack(">II", raw[:8])
+    from ..ops import host
+
+    magic, (n, _, _) = host.idx_info(path)
     if magic != 2049:
         raise ValueError(f"{path}: bad IDX label magic {magic}")
     if max_labels is not None:
         n = min(n, max_labels)
-    a = np.frombuffer(raw, dtype=np.uint8, count=n, offset=8)
-    return torch.from_numpy(a.astype(np.int32))
+    return torch.from_numpy(host.idx_read(path, 0, n, 1).astype(np.int32))
 
 
 def write_idx_images(path, images_u8: torch.Tensor, rows: int = 28, cols: int = 28) -> None:

@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -409,3 +410,60 @@ int cmeh_letter_histogram(const uint8_t* text, size_t n, size_t stride, size_t o
     return 0;
 }
 
+
+// ---- IDX files ---------------------------------------------------------------
+namespace {
+bool read_be32(FILE* f, uint32_t* v) {
+    unsigned char b[4];
+    if (std::fread(b, 1, 4, f) != 4) return false;
+    *v = ((uint32_t)b[0] << 24) | ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | (uint32_t)b[3];
+    return true;
+}
+
+int64_t idx_header(FILE* f, int32_t* magic, int64_t dims[3]) {
+    uint32_t m = 0;
+    if (!read_be32(f, &m)) return -2;
+    const int nd = (int)(m & 0xFF);               // low byte of the magic = number of dimensions
+    if (((m >> 8) & 0xFF) != 0x08 || nd < 1 || nd > 3) return -3;   // 0x08 = unsigned byte payload
+    dims[0] = dims[1] = dims[2] = 1;
+    for (int i = 0; i < nd; ++i) {
+        uint32_t d = 0;
+        if (!read_be32(f, &d)) return -2;
+        dims[i] = d;
+    }
+    if (magic) *magic = (int32_t)m;
+    return 4 + 4 * (int64_t)nd;
+}
+}  // namespace
+
+int64_t cmeh_idx_info(const char* path, int32_t* magic, int64_t dims[3]) {
+    if (!path || !dims) return -1;
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return -4;
+    const int64_t off = idx_header(f, magic, dims);
+    std::fclose(f);
+    return off;
+}
+
+int64_t cmeh_idx_read(const char* path, int64_t first_item, int64_t num_items, uint8_t* dst) {
+    if (!path || !dst || first_item < 0 || num_items < 0) return -1;
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return -4;
+    int64_t dims[3];
+    int32_t magic = 0;
+    const int64_t off = idx_header(f, &magic, dims);
+    if (off < 0) {
+        std::fclose(f);
+        return off;
+    }
+    const int64_t item = dims[1] * dims[2];
+    if (first_item + num_items > dims[0]) {
+        std::fclose(f);
+        return -5;
+    }
+    int64_t got = -2;
+    if (std::fseek(f, (long)(off + first_item * item), SEEK_SET) == 0)
+        got = (int64_t)std::fread(dst, 1, (size_t)(num_items * item), f);
+    std::fclose(f);
+    return got == num_items * item ? got : -2;
+}

@@ -71,6 +71,14 @@ int64_t cmeh_max_ulp_f64(const double* a, const double* b, size_t n, size_t* arg
 int cmeh_letter_histogram(const uint8_t* text, size_t n, size_t stride, size_t offset,
                           uint64_t counts[256]);
 
+/* ---- fpcode: IDX (MNIST) files (ref fpcode/utils/mnist.cpp:9-66) -----------
+ * cmeh_idx_info: magic (2051 images / 2049 labels) and up to 3 big-endian dimensions
+ * (count, rows, cols; rows = cols = 1 for labels); returns the payload offset in bytes,
+ * negative on failure.  cmeh_idx_read: copies `count` payload bytes starting at item
+ * `first_item` (item = rows*cols bytes) into dst; pixels stay raw 0..255 as in the reference. */
+int64_t cmeh_idx_info(const char* path, int32_t* magic, int64_t dims[3]);
+int64_t cmeh_idx_read(const char* path, int64_t first_item, int64_t num_items, uint8_t* dst);
+
 int cmeh_num_threads(void);
 
 #ifdef __cplusplus

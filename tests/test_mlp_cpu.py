@@ -124,6 +124,20 @@ def test_idx_roundtrip(tmp_path):
     assert src == "idx" and torch.equal(x, x2) and torch.equal(lab, lab2) and xt.shape == (10, 784)
     raw = (tmp_path / "train-images-idx3-ubyte").read_bytes()
     assert raw[:4] == b"\x00\x00\x08\x03"              # big-endian magic, ref mnist.cpp:9-18
+    # the native reader: partial reads, bad files
+    from cme213_sp18_b200.ops import host
+
+    assert host.idx_info(tmp_path / "train-images-idx3-ubyte") == (2051, (50, 28, 28))
+    part = host.idx_read(tmp_path / "train-images-idx3-ubyte", 7, 3, 784)
+    assert torch.equal(torch.from_numpy(part).view(3, 784), x[7:10])
+    assert torch.equal(mnist.read_idx_images(tmp_path / "train-images-idx3-ubyte", 5), x[:5])
+    with pytest.raises(ValueError):
+        host.idx_read(tmp_path / "train-images-idx3-ubyte", 48, 3, 784)      # past the end
+    (tmp_path / "junk").write_bytes(b"not an idx file")
+    with pytest.raises(ValueError):
+        host.idx_info(tmp_path / "junk")
+    with pytest.raises(ValueError):
+        mnist.read_idx_labels(tmp_path / "train-images-idx3-ubyte")           # wrong magic
 
 
 def test_save_label_format(tmp_path):
