@@ -122,9 +122,9 @@ def run_ours(args) -> dict:
     e2e = None
     if not args.no_e2e:
         xp, lp = x_host.pin_memory(), lab_host.pin_memory()
-        # one rank: the C++ loop (no Python per step); several ranks: the engine's bucketed
-        # overlap of reduce and backward matters more, which the Python-driven feeder keeps
-        native = args.feeder == "native" or (args.feeder == "auto" and world == 1)
+        # the C++ loop issues the same schedule as the engine (bucketed overlap included) without
+        # Python on the per-step path; --feeder python keeps the Python-driven feeder for comparison
+        native = args.feeder in ("native", "auto") and eng.comm != "nccl"
         feeder = (NativeFeeder if native else StreamingFeeder)(eng, D, graph=not args.no_graph)
         loss_pinned = torch.zeros(max(W, K), dtype=torch.float32).pin_memory()
         batches = lambda n, off: [(((off + i) % pool) * gb, in_proc) for i in range(n)]  # noqa: E731

@@ -389,7 +389,8 @@ def make_mlp_plan(eng):
                     ("params", C.c_void_p * 16), ("grads", C.c_void_p * 16), ("w1c", C.c_void_p * 16),
                     ("xb", C.c_void_p), ("a1", C.c_void_p), ("dz1", C.c_void_p), ("dz2b", C.c_void_p),
                     ("w2c", C.c_void_p), ("w2t", C.c_void_p), ("dz2", C.c_void_p), ("pred", C.c_void_p),
-                    ("pads_dev", C.c_void_p)]
+                    ("pads_dev", C.c_void_p), ("overlap", C.c_int), ("use_mc", C.c_int),
+                    ("grads_mc", C.c_void_p), ("params_mc", C.c_void_p), ("w1c_mc", C.c_void_p)]
 
     p = CmeMlpPlan()
     p.D, p.H, p.C, p.Hp, p.ldx, p.ldh = eng.D, eng.Hh, eng.C, eng.Hp, eng.ldx, eng.ldh
@@ -401,6 +402,11 @@ def make_mlp_plan(eng):
     p.xb, p.a1, p.dz1, p.dz2b = ptr(eng.xb), ptr(eng.a1), ptr(eng.dz1), ptr(eng.dz2b)
     p.w2c, p.w2t, p.dz2, p.pred = ptr(eng.w2c), ptr(eng.w2t), ptr(eng.dz2), ptr(eng.pred)
     p.pads_dev = ptr(eng.pads_dev) if eng.info.world > 1 else None
+    # same bucketing and reduction flavour as the Python-issued step: the owner of every slice of
+    # the sharded fp32 master depends on it
+    p.overlap, p.use_mc = int(eng.overlap), int(eng.use_mc)
+    if eng.use_mc:
+        p.grads_mc, p.params_mc, p.w1c_mc = eng.grads.multicast_ptr, eng.params.multicast_ptr, eng.w1c.multicast_ptr
     return p
 
 
@@ -415,7 +421,9 @@ def mlp_step_native(plan, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: fl
     lib.cme_mlp_step.restype = C.c_int
     check(lib.cme_mlp_step(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
                            stream_ptr()), "cme_mlp_step")
-    _count(9 if plan.nranks == 1 else 11)
+    lib.cme_mlp_step_launches.argtypes = [C.c_void_p]
+    lib.cme_mlp_step_launches.restype = C.c_int
+    _count(lib.cme_mlp_step_launches(C.addressof(plan)))
 
 
 def warmup() -> int:

@@ -288,14 +288,16 @@ class NativeFeeder:
     """Same job as StreamingFeeder with the loop in C++ (csrc/mlp_runtime.cu): one call queues
     every step of the run (H2D on a copy stream, one CUDA graph per step, loss read-back), so
     the Python interpreter is not on the per-step path at all.  The step inside is
-    cme_mlp_step, i.e. the single-stream schedule without the bucketed overlap of
-    MLPEngineBF16; prefer StreamingFeeder when several ranks train a wide layer."""
+    cme_mlp_step_ex, the same schedule MLPEngineBF16 issues (side-stream memset, bucketed
+    overlap of the first half of the W1 reduction with the rest of the backward pass)."""
 
     def __init__(self, engine, D: int, graph: bool = True):
         from ..ops import device as dev
 
         if D != engine.D:
             raise ValueError(f"feeder built for {D} features, the engine has {engine.D}")
+        if engine.comm == "nccl" or engine.tail != "tc":
+            raise ValueError("the native runtime drives the fused tensor-core step only")
         self.eng = engine
         self.rt = dev.MlpRuntime(engine, graphs=graph)
         self.h2d_bytes = 0

@@ -9,7 +9,8 @@
 //   copy stream     H2D of step i+1's uint8 pixels + int32 labels from pinned host memory into
 //                   one of two device staging slots
 //   compute stream  one CUDA graph per (slot, rows, lr, reg, scale) holding the whole step
-//                   (cme_mlp_step: staging, forward, backward, fused all-reduce + SGD, re-cast)
+//                   (cme_mlp_step_ex: staging, forward, backward, fused all-reduce + SGD,
+//                   re-cast; the memset and the first bucket's reduction fork to a side stream)
 //                   and a one-thread kernel that stores the step's summed cross-entropy
 //                   straight into the caller's pinned (device-mapped) loss array.  A
 //                   cudaMemcpyAsync per step for those 4 bytes was measured at +17 us of host
@@ -39,7 +40,8 @@ struct CmeMlpRuntime {
     CmeMlpPlan plan;
     int device = 0;
     int use_graphs = 1;
-    cudaStream_t copy = nullptr, compute = nullptr;
+    cudaStream_t copy = nullptr, compute = nullptr, side = nullptr;
+    cudaEvent_t step_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
     cudaEvent_t join_in = nullptr, join_out = nullptr;
     uint8_t* x_stage[2] = {nullptr, nullptr};
@@ -69,12 +71,13 @@ __global__ void publish_loss_kernel(LossCursor* c, const float* loss) {
     c->next = i + 1;
 }
 
-int kernels_per_step(const CmeMlpPlan& p) { return p.nranks > 1 ? 12 : 10; }
+int kernels_per_step(const CmeMlpPlan& p) { return cme_mlp_step_launches(&p) + 1; }
 
 int issue_step(CmeMlpRuntime* rt, int slot, int64_t rows, float lr, float reg, float scale) {
     CME_CUDA(cudaMemsetAsync(rt->loss_dev + slot, 0, sizeof(float), rt->compute));
-    const int rc = cme_mlp_step(&rt->plan, rt->x_stage[slot], rt->y_stage[slot], rows, lr, reg, scale,
-                                rt->loss_dev + slot, rt->compute);
+    const int rc = cme_mlp_step_ex(&rt->plan, rt->x_stage[slot], rt->y_stage[slot], rows, lr, reg, scale,
+                                   rt->loss_dev + slot, rt->compute, rt->side,
+                                   reinterpret_cast<void* const*>(rt->step_ev));
     if (rc) return rc;
     publish_loss_kernel<<<1, 1, 0, rt->compute>>>(rt->cursor, rt->loss_dev + slot);
     CME_LAUNCH_CHECK();
@@ -131,6 +134,9 @@ int cme_mlp_runtime_destroy(CmeMlpRuntime* rt) {
     cudaSetDevice(rt->device);
     if (rt->compute) cudaStreamSynchronize(rt->compute);
     if (rt->copy) cudaStreamSynchronize(rt->copy);
+    if (rt->side) cudaStreamSynchronize(rt->side);
+    for (auto& e : rt->step_ev)
+        if (e) cudaEventDestroy(e);
     for (auto& kv : rt->graphs) cudaGraphExecDestroy(kv.second);
     for (int s = 0; s < 2; ++s) {
         if (rt->copied[s]) cudaEventDestroy(rt->copied[s]);
@@ -144,6 +150,7 @@ int cme_mlp_runtime_destroy(CmeMlpRuntime* rt) {
     if (rt->cursor) cudaFree(rt->cursor);
     if (rt->copy) cudaStreamDestroy(rt->copy);
     if (rt->compute) cudaStreamDestroy(rt->compute);
+    if (rt->side) cudaStreamDestroy(rt->side);
     cudaSetDevice(prev);
     delete rt;
     return 0;
@@ -162,6 +169,8 @@ int cme_mlp_runtime_create(const CmeMlpPlan* plan, int use_graphs, CmeMlpRuntime
         CME_CUDA(cudaGetDevice(&rt->device));
         CME_CUDA(cudaStreamCreateWithFlags(&rt->copy, cudaStreamNonBlocking));
         CME_CUDA(cudaStreamCreateWithFlags(&rt->compute, cudaStreamNonBlocking));
+        CME_CUDA(cudaStreamCreateWithFlags(&rt->side, cudaStreamNonBlocking));
+        for (auto& e : rt->step_ev) CME_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (int s = 0; s < 2; ++s) {
             CME_CUDA(cudaEventCreateWithFlags(&rt->copied[s], cudaEventDisableTiming));
             CME_CUDA(cudaEventCreateWithFlags(&rt->consumed[s], cudaEventDisableTiming));

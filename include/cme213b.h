@@ -277,15 +277,34 @@ typedef struct CmeMlpPlan {
     float* dz2;
     int32_t* pred;
     uint32_t* const* pads_dev;
+    /* Optional, zero = off.  overlap: with more than one rank, W1 rows [0, hs) are reduced as a
+     * bucket of their own (on the side stream when one is given) while the rest of the backward
+     * pass runs; hs = cme_mlp_split_point().  The flag also fixes which rank owns which slice of
+     * the sharded fp32 master, so it must not change during a run.  use_mc: reduce through the
+     * NVSwitch multicast mappings below (cme_allreduce_sgd_mc) instead of peer loads. */
+    int overlap, use_mc;
+    const float* grads_mc;
+    float* params_mc;
+    void* w1c_mc;
 } CmeMlpPlan;
 /* One whole training step on `rows` local samples (uint8 pixels x_u8 [rows][D], labels
  * int32 [rows], both device pointers; x_u8 may be peer-mapped): staging, forward, backward,
- * fused all-reduce + L2 + SGD, bf16 re-cast, all on `stream` with no host synchronisation.
+ * fused all-reduce + L2 + SGD, bf16 re-cast, with no host synchronisation.
  * scale = 1 / (global samples in the minibatch); loss_sum (may be NULL) += cross-entropy.
  * The C++ counterpart of one iteration of parallel_train's loop
- * (ref fpcode/neural_network.cpp:484-541). */
+ * (ref fpcode/neural_network.cpp:484-541).  cme_mlp_step issues everything on `stream`;
+ * cme_mlp_step_ex also takes a side stream and 4 cudaEvent_t (disable-timing is fine) and
+ * moves the gradient memset and the first bucket's reduction there; both are capturable
+ * into a CUDA graph from `stream`. */
 int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
                  float lr, float reg, float scale, float* loss_sum, void* stream);
+int cme_mlp_step_ex(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels,
+                    int64_t rows, float lr, float reg, float scale, float* loss_sum, void* stream,
+                    void* side_stream, void* const* events);
+/* First hidden unit of the second bucket (0 = the step is not split). */
+int cme_mlp_split_point(const CmeMlpPlan* plan);
+/* Kernels one step launches (memsets not counted). */
+int cme_mlp_step_launches(const CmeMlpPlan* plan);
 
 /* Native streaming trainer (csrc/mlp_runtime.cu): the C++ counterpart of parallel_train's
  * whole minibatch loop (ref fpcode/neural_network.cpp:443-567) for data that lives in pinned

@@ -166,6 +166,48 @@ shutdown()
     assert "TWO_GPU_OK" in res.stdout
 
 
+@pytest.mark.multigpu
+@pytest.mark.timeout(400)
+def test_two_gpu_native_runtime_matches_python_engine(tmp_path):
+    """The C++ loop on 2 ranks (bucketed overlap active at H = 1024; peer-load and multicast
+    reductions) against the Python-driven resident trainer, through parallel_train."""
+    script = tmp_path / "worker.py"
+    script.write_text(f"""
+import sys, torch
+sys.path.insert(0, {str(ROOT)!r})
+from cme213_sp18_b200.models import mlp as M
+from cme213_sp18_b200.parallel.dist import init_distributed, shutdown
+from cme213_sp18_b200.parallel.dp_trainer import parallel_train
+from cme213_sp18_b200.utils import mnist
+info = init_distributed()
+x, lab = mnist.synthetic_mnist(2900, seed=0, pixel_max=1)       # short last batch: 500 of 800
+base = M.NeuralNetwork([784, 1024, 10])
+out = {{}}
+for name, kw in (("resident", dict(comm="fused", data_mode="sharded")),
+                 ("stream_p2p", dict(comm="p2p", data_mode="stream")),
+                 ("stream_mc", dict(comm="mc", data_mode="stream"))):
+    nn = base.clone()
+    r = parallel_train(nn, x, lab, 0.1, 1e-4, 2, 800, info=info, print_every=3, log=lambda *_: None, **kw)
+    out[name] = (nn, r)
+ref = out["resident"][0]
+for name in ("stream_p2p", "stream_mc"):
+    nn, r = out[name]
+    for a, b in zip(nn.W + nn.b, ref.W + ref.b):
+        d = (a - b).abs().max() / b.abs().max()
+        assert d < 2e-3, (name, float(d))
+    assert r["iterations"] == 8 and [it for it, _ in r["losses"]] == [0, 3, 6], r
+    # rank-local loss of the streamed run against the global mean of the resident run
+    for (_, a), (_, b) in zip(r["losses"], out["resident"][1]["losses"]):
+        assert a > 0 and abs(a - b) < 0.25 * b, (name, r["losses"], out["resident"][1]["losses"])
+if info.rank == 0:
+    print("TWO_GPU_NATIVE_OK")
+shutdown()
+""")
+    res = _torchrun(script, 2, 29543)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "TWO_GPU_NATIVE_OK" in res.stdout
+
+
 def test_streaming_feeder_matches_resident_training():
     """The end-to-end path (pinned host -> device every step, loss read back every step) must
     train exactly like the device-resident path, including under CUDA-graph replay."""
