@@ -361,10 +361,10 @@ gemm_kmajor_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 // reads the two halves of B from both CTAs' shared memory.  Each CTA keeps its 128 x 256
 // accumulator in its own TMEM and runs its own epilogue.
 constexpr int kStages2 = 6;                  // MN-major pair kernel: no output staging
-constexpr int kStagesK2 = 5;                 // K-major pair kernel: one stage less, four staging buffers
+constexpr int kStagesK2 = 6;                 // K-major pair kernel: six stages + two output staging buffers
 constexpr int kThreadsK2 = 320;              // producer warp + MMA warp + 8 epilogue warps
 constexpr int kB2Bytes = 128 * BK * 2;       // this CTA's half of the B tile: 16 KB
-constexpr int kSmemKMajor2 = kStagesK2 * (kABytes + kB2Bytes) + 4 * kStageBytes + 1024 + 256;
+constexpr int kSmemKMajor2 = kStagesK2 * (kABytes + kB2Bytes) + 2 * kStageBytes + 1024 + 256;
 constexpr int kSmemMNMajor2 = kStages2 * (kABytes + kB2Bytes) + 1024 + 256;
 
 struct Barriers2 {
@@ -375,11 +375,14 @@ struct Barriers2 {
     uint32_t tmem_base;
 };
 
-// The epilogue (TMEM -> sigmoid -> bf16 -> swizzled smem -> TMA store of 128 x 256 outputs per
-// CTA and tile) was the limiter with four warps (ncu: tensor pipe 65 % busy).  Eight epilogue
-// warps work as two groups, each owning two of the four 64-column chunks with its own pair of
-// staging buffers, named barrier and TMA-store leader; the sigmoid is evaluated two at a time
-// (tanh.approx.bf16x2).
+// Epilogue: TMEM -> sigmoid -> bf16 -> swizzled smem -> TMA store of 128 x 256 outputs per CTA
+// and tile.  Eight epilogue warps work as two groups, each owning two of the four 64-column
+// chunks with its own staging buffer, named barrier and TMA-store leader; the sigmoid is
+// evaluated two at a time (tanh.approx.bf16x2).  The main loop, not the epilogue, sets the
+// pace (profiles/fwd1_probe.md): with every epilogue instruction removed the 65536 x 8192 x 785
+// product still takes 0.61-0.63 ms (0.70-0.71 with the epilogue; cuBLAS 0.63), and that floor
+// does not move with the ring depth (5 or 6 stages), the tile order, the operand layout or
+// even when every load hits the same lines, so it is not operand delivery.
 template <int EPI /* 0 = identity, 1 = sigmoid */>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsK2, 1)
 gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -389,7 +392,7 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint8_t* sA = smem;
     uint8_t* sB = sA + kStagesK2 * kABytes;
     uint8_t* sC = sB + kStagesK2 * kB2Bytes;
-    Barriers2* bars = (Barriers2*)(sC + 4 * kStageBytes);
+    Barriers2* bars = (Barriers2*)(sC + 2 * kStageBytes);
     constexpr int BN = 256;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -472,10 +475,9 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int grp = (warp - 2) >> 2;                 // 0: chunks 0,1   1: chunks 2,3
         const int row = q * 32 + lane;
         const bool leader = (((warp - 2) & 3) == 0 && lane == 0);
-        uint8_t* my_stage = sC + grp * 2 * kStageBytes;
+        uint8_t* stg = sC + grp * kStageBytes;           // one staging buffer per group
         int acc = 0;
         uint32_t acc_phase = 0;
-        int cbuf = 0;
         for (int tile = pair; tile < num_tiles; tile += npairs) {
             const int m0 = (tile / n_tiles) * 256 + (int)cta * 128;
             const int n0 = (tile % n_tiles) * BN;
@@ -485,29 +487,26 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int cc = 0; cc < 2; ++cc) {
                 const int c = grp * 2 + cc;
-                if (leader) tma_store_wait_read<1>();
-                named_bar_sync(1 + grp, 128);
-                uint8_t* stg = my_stage + cbuf * kStageBytes;
                 uint32_t v0[32], v1[32];
                 tmem_ld_32x32(t_row + (uint32_t)(c * 64), v0);
                 tmem_ld_32x32(t_row + (uint32_t)(c * 64 + 32), v1);
                 tmem_ld_wait();
+                // 64 outputs of this thread's row, packed, before the staging buffer is needed
+                uint32_t pk[32];
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    const uint32_t* v = half ? v1 : v0;
+                for (int e = 0; e < 16; ++e) {
+                    const float a0 = __uint_as_float(v0[2 * e]), a1 = __uint_as_float(v0[2 * e + 1]);
+                    const float b0 = __uint_as_float(v1[2 * e]), b1 = __uint_as_float(v1[2 * e + 1]);
+                    pk[e] = (EPI == 1) ? sigmoid2_bf16(a0, a1) : pack_bf16(a0, a1);
+                    pk[16 + e] = (EPI == 1) ? sigmoid2_bf16(b0, b1) : pack_bf16(b0, b1);
+                }
+                if (leader) tma_store_wait_read<0>();    // the previous chunk has left the buffer
+                named_bar_sync(1 + grp, 128);
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        uint32_t p[4];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float x0 = __uint_as_float(v[g * 8 + 2 * e]);
-                            const float x1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
-                            p[e] = (EPI == 1) ? sigmoid2_bf16(x0, x1) : pack_bf16(x0, x1);
-                        }
-                        const int chunk = half * 4 + g;
-                        const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
-                        *reinterpret_cast<uint4*>(stg + off) = make_uint4(p[0], p[1], p[2], p[3]);
-                    }
+                for (int chunk = 0; chunk < 8; ++chunk) {
+                    const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+                    *reinterpret_cast<uint4*>(stg + off) =
+                        make_uint4(pk[4 * chunk], pk[4 * chunk + 1], pk[4 * chunk + 2], pk[4 * chunk + 3]);
                 }
                 fence_proxy_async_smem();
                 named_bar_sync(1 + grp, 128);
@@ -515,7 +514,6 @@ gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     tma_store_2d(&tmC, stg, n0 + c * 64, m0);
                     tma_store_commit();
                 }
-                cbuf ^= 1;
             }
             tc_fence_before();
             __syncwarp();
