@@ -381,8 +381,9 @@ struct Barriers2 {
 // evaluated two at a time (tanh.approx.bf16x2).  The main loop, not the epilogue, sets the
 // pace (profiles/fwd1_probe.md): with every epilogue instruction removed the 65536 x 8192 x 785
 // product still takes 0.61-0.63 ms (0.70-0.71 with the epilogue; cuBLAS 0.63), and that floor
-// does not move with the ring depth (5 or 6 stages), the tile order, the operand layout or
-// even when every load hits the same lines, so it is not operand delivery.
+// does not move with the ring depth (5 or 6 stages), the operand layout, the accumulator
+// hand-over between tiles, or even when every load hits the same lines: 1.43 PFLOP/s, the rate
+// this board sustains on bf16 MMAs under its power limit (cuBLAS: 1.38 PFLOP/s).
 template <int EPI /* 0 = identity, 1 = sigmoid */>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsK2, 1)
 gemm_kmajor2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
