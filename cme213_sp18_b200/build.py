@@ -122,7 +122,13 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
             flags = [f for f in HOST_FLAGS if f != "-fopenmp"]
             sys.stderr.write("[build] OpenMP unavailable, building the host library serial\n")
             _run([cxx, *flags, "-shared", "-o", str(host_lib), *map(str, host_srcs)], None, verbose)
-    return {"device": dev_lib, "host": host_lib}
+    # --- C++ example: a trainer that uses the C ABI only (no Python, no torch) ---
+    ex_src = ROOT / "examples" / "train_mlp.cpp"
+    ex_bin = LIBDIR / "train_mlp_example"
+    if ex_src.exists() and (force or _newer(ex_bin, [ex_src, dev_lib] + headers)):
+        _run([nvcc, "-O2", "-std=c++17", "-I", str(INC), str(ex_src), "-o", str(ex_bin),
+              "-L", str(LIBDIR), "-lcme213b", "-Xlinker", "-rpath=$ORIGIN"], None, verbose)
+    return {"device": dev_lib, "host": host_lib, "example": ex_bin}
 
 
 def main(argv=None) -> int:

@@ -90,3 +90,15 @@ def test_two_gpu_heat_slabs_and_pagerank(tmp_path):
     assert r.returncode == 0 and "beyond 512 ULP" not in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
     p = run_module("cme213_sp18_b200.cli.pagerank", "--nodes", "200000", "--avg", "6", cwd=tmp_path, nproc=2, port=29573)
     assert p.returncode == 0 and "ranks=2" in p.stdout and "ok" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+
+
+def test_cpp_example_trains_without_python():
+    """examples/train_mlp.cpp: the C ABI alone (cme_mlp_runtime_*) trains the MLP from a C++ program."""
+    from cme213_sp18_b200 import build
+
+    exe = build.build()["example"]
+    res = subprocess.run([str(exe), "256", "1024", "6", "8192", "0.3"], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "TRAIN_OK" in res.stdout
+    acc = float(res.stdout.split("accuracy")[1].split()[0])
+    assert acc > 0.8, res.stdout
