@@ -26,4 +26,4 @@ sass: build
 	bash scripts/dump_sass.sh
 
 clean:
-	rm -rf build cme213_sp18_b200/lib/*.so baseline/_ref
+	rm -rf build cme213_sp18_b200/lib/*.so cme213_sp18_b200/lib/train_mlp_example baseline/_ref

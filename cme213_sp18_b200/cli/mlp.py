@@ -41,7 +41,11 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("-s", dest="run_seq", action="store_true")
     ap.add_argument("-d", dest="debug", action="store_true")
     ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp64"])
-    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--comm", default="fused", choices=["fused", "p2p", "mc", "nccl"])
+    ap.add_argument("--data-mode", default="owner", choices=["owner", "sharded", "stream"],
+                    help="owner: rank 0 uploads the dataset once and ranks pull their slices over NVLink "
+                         "(the reference's scatter); sharded: every rank uploads it; stream: it stays in "
+                         "pinned host memory and the C++ runtime feeds every step")
     ap.add_argument("--data-dir", default="data")
     ap.add_argument("--train-size", type=int, default=mnist.NUM_TRAIN)
     ap.add_argument("--test-size", type=int, default=mnist.NUM_TEST)
@@ -108,8 +112,8 @@ def main(argv=None) -> int:
         precision = "fp64" if (args.grade or args.debug) else "bf16"
     dl = grading.CpuGpuDiffLog(out / "CpuGpuDiff.txt", out / "CPUmats") if (args.debug and rank0) else None
     t0 = time.perf_counter()
-    if info.device.type == "cpu" and info.world > 1:
-        # the gloo schedule wants the data on every rank
+    if (info.device.type == "cpu" or args.data_mode != "owner") and info.world > 1:
+        # the gloo schedule and the sharded / stream modes want the data on every rank
         import torch.distributed as dist
 
         box = [x_train, l_train]
@@ -117,6 +121,7 @@ def main(argv=None) -> int:
         x_train, l_train = box
     parallel_train(nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
                    args.print_every, args.debug, info=info, precision=precision, comm=args.comm,
+                   data_mode=args.data_mode if precision == "bf16" or args.data_mode != "stream" else "owner",
                    debug_log=dl)
     if rank0:
         print(f"Time for Parallel Training: {time.perf_counter() - t0} seconds")

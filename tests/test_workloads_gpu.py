@@ -79,6 +79,16 @@ def test_mlp_cli_grade3_gpu(tmp_path):
     assert len(rows) >= 2 and all(float(v) < 1e-7 for v in rows[1].split()[1:])
 
 
+def test_mlp_cli_stream_mode(tmp_path):
+    """The reference's command line with the dataset kept in host memory (C++ feeding runtime)."""
+    r = run_module("cme213_sp18_b200.cli.mlp", "-n", "128", "-l", "0.3", "-e", "4", "-b", "500", "-p", "10",
+                   "--pixel-max", "1", "--data-mode", "stream", "--train-size", "6000", "--test-size", "100",
+                   "--data-dir", tmp_path / "none", "--outdir", tmp_path / "Outputs", cwd=tmp_path)
+    assert r.returncode == 0, r.stdout + r.stderr
+    prec = float(r.stdout.split("Precision on validation set for parallel training =")[1].split()[0])
+    assert prec > 0.9, r.stdout
+
+
 @pytest.mark.multigpu
 def test_two_gpu_heat_slabs_and_pagerank(tmp_path):
     (tmp_path / "params.in").write_text("300 256\n1 1\n40\n8\n")
