@@ -63,7 +63,7 @@ class MLPEngineBF16:
         self.pred = torch.zeros(max_rows, dtype=torch.int32, device=d)
         self.loss = torch.zeros(1, dtype=torch.float32, device=d)
         # NVSwitch multicast (multimem.ld_reduce / multimem.st) wins from 4 ranks up (measured:
-        # 0.449 vs 0.480 ms/step at 8 ranks, 0.708 vs 0.720 at 4, slightly slower at 2)
+        # 0.401 vs 0.434 ms/step at 8 ranks, a few percent at 4, slightly slower at 2)
         want_mc = comm == "mc" or (comm == "fused" and self.info.world >= 4)
         self.use_mc = bool(want_mc and self.info.world > 1 and self.grads.multicast_ptr
                            and self.params.multicast_ptr and self.w1c.multicast_ptr)
