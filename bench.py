@@ -147,6 +147,36 @@ def run_ours(args) -> dict:
                "last_loss_per_sample": float(loss_pinned[K - 1]) / in_proc,
                "feeder": "native (cme_mlp_runtime_run)" if native else "python (StreamingFeeder)"}
 
+    # ---- exposed communication: the same per-rank work on an engine that has no peers ----
+    exposed = None
+    if world > 1:
+        from cme213_sp18_b200.models.mlp_engine import MLPEngineBF16
+        from cme213_sp18_b200.parallel.dist import DistInfo
+
+        solo = MLPEngineBF16(H, in_proc, DistInfo(device=info.device))
+        solo.load_params(nn)
+
+        def solo_step(i):
+            p = i % pool
+            solo.step(x_dev[p].data_ptr(), l_dev[p], in_proc, args.lr, args.reg, in_proc * world,
+                      graph=not args.no_graph)
+
+        for i in range(pool + W):
+            solo_step(i)
+        torch.cuda.synchronize()
+        barrier(info)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(K):
+            solo_step(W + i)
+        s1.record()
+        torch.cuda.synchronize()
+        barrier(info)
+        ms_solo = max_over_ranks_ms(s0.elapsed_time(s1))
+        exposed = {"ms_per_step_without_peers": ms_solo / K,
+                   "exposed_allreduce_ms_per_step": max(0.0, (ms - ms_solo) / K)}
+        del solo
+
     breakdown = None
     if args.breakdown:
         names = ["stage", "zero_grads", "fwd1", "fwd2_softmax", "backward", "allreduce_sgd+barriers", "recast_w2"]
@@ -187,6 +217,8 @@ def run_ours(args) -> dict:
         "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
         "tflops": value * M.flops_per_sample(H) / 1e12,
     }
+    if exposed:
+        out["communication"] = exposed
     if breakdown:
         out["breakdown_ms"] = breakdown
     if dist.is_initialized():
