@@ -2,7 +2,7 @@
 # SASS evidence for the Blackwell-native kernels: mnemonic counts per object file into profiles/sass/.
 cd "$(dirname "$0")/.."
 mkdir -p profiles/sass
-for f in gemm_tc comm stencil pagerank mlp_elem; do
+for f in gemm_tc comm stencil pagerank mlp_elem mlp_runtime; do
   cuobjdump -sass build/obj/$f.o > /tmp/$f.sass 2>/dev/null
   {
     echo "# $f.cu — SASS mnemonic counts (cuobjdump -sass build/obj/$f.o, sm_100a)"
