@@ -44,6 +44,8 @@ void set_error(const char* fmt, ...);
 
 // Cached per-process device facts (queried once for the current device).
 int sm_count();
+// cuTensorMapEncodeTiled from the driver (no link-time dependency on libcuda); null if absent.
+void* tensor_map_encoder();
 
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

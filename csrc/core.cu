@@ -28,6 +28,19 @@ int sm_count() {
     return cached[dev];
 }
 
+void* tensor_map_encoder() {
+    static void* fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = p;
+    });
+    return fn;
+}
+
 }  // namespace cme
 
 namespace {

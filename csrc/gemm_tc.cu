@@ -1258,18 +1258,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
-                cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)p;
-    });
-    return fn;
-}
+EncodeTiledFn encode_fn() { return reinterpret_cast<EncodeTiledFn>(cme::tensor_map_encoder()); }
 
 // 2-D bf16 tensor map: dims {inner, outer}, row pitch ld elements, 128-byte swizzle
 int make_map(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,

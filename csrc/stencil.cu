@@ -13,6 +13,10 @@
 // The slab kernel adds the multi-GPU piece: edge rows are stored directly into
 // the neighbours' ghost rows over NVLink from inside the sweep.
 #include "common.cuh"
+#include "tc_common.cuh"
+
+#include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -142,15 +146,173 @@ sweep_loop(float* __restrict__ next, const float* __restrict__ curr, int gx, int
     }
 }
 
-// ---- variant 2: shared-memory tile + register marching ---------------------------
-// A block of 256 threads owns a tile of kTX x kTY interior points.  The tile and its
-// halo are staged in shared memory once (one barrier per tile); each thread then owns
-// one column of kRY consecutive rows and marches down it with the 2R+1 vertical
-// neighbours in registers, taking the x neighbours from the shared row.  Per output:
-// one new shared load for the window plus 2R+1 for the row, no global re-reads.  If
-// push_* pointers are set, the rows listed as edge rows are also stored to a
-// neighbour GPU.
-constexpr int kTX = 64, kTY = 64, kRY = 16;   // 64 x 4 threads, 16 rows per thread
+// ---- variant 2: shared-memory tile, four columns per thread, register marching -----------
+// A block of 256 threads owns a tile of kTX x kTY interior points.  The tile and its halo are
+// staged in shared memory once (128-bit loads, one barrier per tile).  A thread owns four
+// adjacent columns and kRY consecutive rows: it marches down with the 2R+1 vertical neighbours
+// of its four columns in registers (one 128-bit shared load per new row) and takes the x
+// neighbours of the centre row with three more (order 8).  That is 5 shared-memory wavefronts
+// per 32 points where one column per thread with scalar loads needed 18: the first version of
+// this kernel was bound by shared-memory load issue (3.3 TB/s of grid traffic, 51 % of the
+// HBM copy rate).  If push_* pointers are set, the rows listed as edge rows are also stored to
+// a neighbour GPU.
+constexpr int kTX = 128, kTY = 64, kRY = 8;   // 32 x 8 threads, 4 columns x 8 rows per thread
+
+template <int R>
+constexpr int tile_pitch() { return (kTX + 2 * R + 3) / 4 * 4; }   // rows stay 16-byte aligned
+
+// four floats starting at column c (any alignment) of a 16-byte aligned shared row
+template <int R>
+__device__ __forceinline__ float4 lds4_at_r(const float* __restrict__ row, int c4) {
+    // c4 is a multiple of 4; the four values start at row[c4 + R]
+    if constexpr (R % 4 == 0) {
+        return *reinterpret_cast<const float4*>(row + c4 + R);
+    } else if constexpr (R % 2 == 0) {
+        const float2 lo = *reinterpret_cast<const float2*>(row + c4 + R);
+        const float2 hi = *reinterpret_cast<const float2*>(row + c4 + R + 2);
+        return make_float4(lo.x, lo.y, hi.x, hi.y);
+    } else {
+        const float4 a = *reinterpret_cast<const float4*>(row + c4);
+        const float4 b4 = *reinterpret_cast<const float4*>(row + c4 + 4);
+        const float t[8] = {a.x, a.y, a.z, a.w, b4.x, b4.y, b4.z, b4.w};
+        return make_float4(t[R % 4], t[R % 4 + 1], t[R % 4 + 2], t[R % 4 + 3]);
+    }
+}
+
+__device__ __forceinline__ float f4_get(const float4& v, int j) {
+    return j == 0 ? v.x : j == 1 ? v.y : j == 2 ? v.z : v.w;
+}
+
+// four results of one row to `dst` (points x .. x+3, the first `nvalid` exist)
+__device__ __forceinline__ void store_quad(float* __restrict__ dst, const float (&v)[4], int nvalid,
+                                           bool vec_ok) {
+    if (vec_ok && nvalid == 4) {
+        *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < nvalid) dst[j] = v[j];
+    }
+}
+
+// global -> shared staging of one tile with its halo (the non-TMA path)
+template <int ORDER>
+__device__ __forceinline__ void tile_fill(const float* __restrict__ curr, int gx, int gy_local, int x0,
+                                          int y0, float* smem) {
+    constexpr int R = ORDER / 2;
+    constexpr int W = tile_pitch<R>(), HT = kTY + 2 * R;
+    const int tid = threadIdx.x;
+    // interior point (x, y) lives at grid (x + R, y + R): the tile with its halo starts at
+    // grid column x0 and grid row y0
+    const bool rows_aligned = (gx % 4 == 0) && ((reinterpret_cast<uintptr_t>(curr) & 15) == 0);
+    if (rows_aligned) {
+        constexpr int W4 = W / 4;
+        for (int i = tid; i < W4 * HT; i += 256) {
+            const int r = i / W4, c = (i - r * W4) * 4;
+            const int gr = y0 + r, gc = x0 + c;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gr < gy_local) {
+                const float* src = curr + (size_t)gr * gx + gc;
+                if (gc + 3 < gx) {
+                    v = __ldg(reinterpret_cast<const float4*>(src));
+                } else {
+                    if (gc < gx) v.x = src[0];
+                    if (gc + 1 < gx) v.y = src[1];
+                    if (gc + 2 < gx) v.z = src[2];
+                }
+            }
+            *reinterpret_cast<float4*>(smem + r * W + c) = v;
+        }
+    } else {
+        for (int i = tid; i < W * HT; i += 256) {
+            const int r = i / W, c = i - r * W;
+            const int gr = y0 + r, gc = x0 + c;
+            smem[i] = (gr < gy_local && gc < gx) ? curr[(size_t)gr * gx + gc] : 0.f;
+        }
+    }
+}
+
+// the marching phase: every thread computes its 4 x kRY points from the staged tile
+template <int ORDER>
+__device__ __forceinline__ void tile_march(float* __restrict__ next, int gx, int x0, int y0, int nx,
+                                           int ny_local, float xcfl, float ycfl,
+                                           float* __restrict__ push_up, int push_up_rows,
+                                           float* __restrict__ push_down, int push_down_from,
+                                           const float* smem) {
+    constexpr int R = ORDER / 2;
+    constexpr int W = tile_pitch<R>();
+    constexpr int XW = (4 + 2 * R + 3) / 4;          // float4s covering the x window of a quad
+    const int tid = threadIdx.x;
+    const int c4 = (tid & 31) * 4, tyg = tid >> 5;
+    const int x = x0 + c4;
+    if (x >= nx) return;
+    const int yb = tyg * kRY;                        // first row of this thread inside the tile
+    // 16-byte stores need the output row start and R to be multiples of 4 floats
+    const bool st_vec = (R % 4 == 0) && (gx % 4 == 0) && ((reinterpret_cast<uintptr_t>(next) & 15) == 0);
+    float4 win[2 * R + 1];                           // vertical neighbours of the four columns
+#pragma unroll
+    for (int k = 0; k < 2 * R; ++k) win[k + 1] = lds4_at_r<R>(smem + (yb + k) * W, c4);
+    const float* srow = smem + (yb + R) * W + c4;    // centre row of the first output
+    const float* vrow = smem + (yb + 2 * R) * W;     // row entering the vertical window
+    float* outp = next + (size_t)gx * (y0 + yb + R) + (x + R);
+
+    // one output row of four points from the registers + the centre row's x window
+    auto quad = [&](float (&out)[4]) {
+        float xw[4 * XW];
+#pragma unroll
+        for (int q = 0; q < XW; ++q) {
+            const float4 t = *reinterpret_cast<const float4*>(srow + 4 * q);
+            xw[4 * q] = t.x, xw[4 * q + 1] = t.y, xw[4 * q + 2] = t.z, xw[4 * q + 3] = t.w;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float xv[2 * R + 1], yv[2 * R + 1];
+#pragma unroll
+            for (int k = 0; k <= 2 * R; ++k) {
+                xv[k] = xw[j + k];
+                yv[k] = f4_get(win[k], j);
+            }
+            out[j] = combine<ORDER>(xv, yv, xcfl, ycfl);
+        }
+    };
+
+    // Tiles that lie fully inside the grid and push nothing take a loop without any bounds
+    // test or address arithmetic beyond three pointer increments per row.
+    const bool pushes = (push_up && y0 < push_up_rows) || (push_down && y0 + kTY > push_down_from);
+    if (st_vec && !pushes && x0 + kTX <= nx && y0 + kTY <= ny_local) {
+#pragma unroll
+        for (int i = 0; i < kRY; ++i) {
+#pragma unroll
+            for (int k = 0; k < 2 * R; ++k) win[k] = win[k + 1];
+            win[2 * R] = lds4_at_r<R>(vrow, c4);
+            float out[4];
+            quad(out);
+            *reinterpret_cast<float4*>(outp) = make_float4(out[0], out[1], out[2], out[3]);
+            srow += W, vrow += W, outp += gx;
+        }
+        return;
+    }
+    const int nvalid = min(4, nx - x);
+    const bool up_vec = st_vec && ((reinterpret_cast<uintptr_t>(push_up) & 15) == 0);
+    const bool dn_vec = st_vec && ((reinterpret_cast<uintptr_t>(push_down) & 15) == 0);
+#pragma unroll
+    for (int i = 0; i < kRY; ++i) {
+#pragma unroll
+        for (int k = 0; k < 2 * R; ++k) win[k] = win[k + 1];
+        win[2 * R] = lds4_at_r<R>(vrow, c4);
+        const int y = y0 + yb + i;
+        if (y < ny_local) {
+            float out[4];
+            quad(out);
+            store_quad(outp, out, nvalid, st_vec);
+            if (push_up && y < push_up_rows)
+                store_quad(push_up + (size_t)gx * y + (x + R), out, nvalid, up_vec);
+            if (push_down && y >= push_down_from)
+                store_quad(push_down + (size_t)gx * (y - push_down_from) + (x + R), out, nvalid, dn_vec);
+        }
+        srow += W, vrow += W, outp += gx;
+    }
+}
 
 template <int ORDER>
 __device__ __forceinline__ void tile_compute(float* __restrict__ next,
@@ -159,43 +321,10 @@ __device__ __forceinline__ void tile_compute(float* __restrict__ next,
                                              float ycfl, float* __restrict__ push_up,
                                              int push_up_rows, float* __restrict__ push_down,
                                              int push_down_from, float* smem) {
-    constexpr int R = ORDER / 2;
-    constexpr int W = kTX + 2 * R, HT = kTY + 2 * R;
-    const int tid = threadIdx.x;
-    // interior point (x, y) lives at grid (x + R, y + R): the tile with its halo starts at
-    // grid column x0 and grid row y0
-    for (int i = tid; i < W * HT; i += 256) {
-        const int r = i / W, c = i - r * W;
-        const int gr = y0 + r, gc = x0 + c;
-        smem[i] = (gr < gy_local && gc < gx) ? curr[(size_t)gr * gx + gc] : 0.f;
-    }
+    tile_fill<ORDER>(curr, gx, gy_local, x0, y0, smem);
     __syncthreads();
-    const int tx = tid & (kTX - 1), tyg = tid / kTX;
-    const int x = x0 + tx;
-    if (x >= nx) return;
-    const int yb = tyg * kRY;                       // first row of this thread inside the tile
-    const float* colp = smem + (size_t)yb * W + tx + R;
-    float win[2 * R + 1];
-#pragma unroll
-    for (int k = 0; k < 2 * R; ++k) win[k + 1] = colp[k * W];
-#pragma unroll
-    for (int i = 0; i < kRY; ++i) {
-#pragma unroll
-        for (int k = 0; k < 2 * R; ++k) win[k] = win[k + 1];
-        win[2 * R] = colp[(i + 2 * R) * W];
-        const int y = y0 + yb + i;
-        if (y < ny_local) {
-            const float* rowp = smem + (size_t)(yb + i + R) * W + tx;
-            float xv[2 * R + 1];
-#pragma unroll
-            for (int k = 0; k <= 2 * R; ++k) xv[k] = rowp[k];
-            const float v = combine<ORDER>(xv, win, xcfl, ycfl);
-            next[(size_t)gx * (y + R) + (x + R)] = v;
-            if (push_up && y < push_up_rows) push_up[(size_t)gx * y + (x + R)] = v;
-            if (push_down && y >= push_down_from)
-                push_down[(size_t)gx * (y - push_down_from) + (x + R)] = v;
-        }
-    }
+    tile_march<ORDER>(next, gx, x0, y0, nx, ny_local, xcfl, ycfl, push_up, push_up_rows, push_down,
+                      push_down_from, smem);
 }
 
 template <int ORDER>
@@ -203,7 +332,7 @@ __global__ void __launch_bounds__(256)
 sweep_shared(float* __restrict__ next, const float* __restrict__ curr, int gx, int gy, float xcfl,
              float ycfl, int tiles_x, int tiles, int bc, float s) {
     constexpr int R = ORDER / 2;
-    __shared__ float smem[(kTX + 2 * R) * (kTY + 2 * R)];
+    __shared__ __align__(16) float smem[tile_pitch<R>() * (kTY + 2 * R)];
     const int nx = gx - 2 * R, ny = gy - 2 * R;
     if ((int)blockIdx.x >= tiles) {
         if (!bc) return;
@@ -219,6 +348,64 @@ sweep_shared(float* __restrict__ next, const float* __restrict__ curr, int gx, i
                         nullptr, 0, smem);
 }
 
+// ---- variant 2 on TMA: persistent blocks, tiles prefetched by the copy engine -------------
+// ncu on sweep_shared: 60 % of the warp stalls are the global loads of the staging loop, with
+// DRAM at 46 % and the issue slots at 46 %: four resident blocks per SM do not hide it.  Here
+// one cp.async.bulk.tensor per tile brings the (kTX + 2R) x (kTY + 2R) box, halo and
+// out-of-range zeros included, into one of two shared buffers while the block computes the
+// other; nothing in the block waits on a global load.  Needs 16-byte aligned rows (gx % 4 == 0).
+template <int R>
+constexpr int tma_smem_bytes() { return 2 * tile_pitch<R>() * (kTY + 2 * R) * 4 + 256; }
+
+template <int ORDER>
+__global__ void __launch_bounds__(256)
+sweep_tma(const __grid_constant__ CUtensorMap tm, float* __restrict__ next,
+          const float* __restrict__ curr, int gx, int gy, float xcfl, float ycfl, int tiles_x,
+          int tiles, int bc, float s) {
+    constexpr int R = ORDER / 2;
+    constexpr int W = tile_pitch<R>(), HT = kTY + 2 * R;
+    constexpr uint32_t kTileBytes = W * HT * 4;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    uint64_t* full = reinterpret_cast<uint64_t*>(base + 2 * kTileBytes);
+    const int nx = gx - 2 * R, ny = gy - 2 * R;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        tc::prefetch_tmap(&tm);
+        tc::mbar_init(&full[0], 1);
+        tc::mbar_init(&full[1], 1);
+        tc::fence_barrier_init();
+    }
+    __syncthreads();
+    int t = blockIdx.x;
+    uint32_t b = 0, phases = 0;                      // current buffer, one parity bit per buffer
+    if (t < tiles && tid == 0) {
+        tc::mbar_expect_tx(&full[0], kTileBytes);
+        tc::tma_load_2d(base, &tm, &full[0], (t % tiles_x) * kTX, (t / tiles_x) * kTY);
+    }
+    for (; t < tiles; t += gridDim.x) {
+        const int tn = t + gridDim.x;
+        if (tn < tiles && tid == 0) {
+            // the other buffer was last read before the barrier that ended the previous iteration
+            tc::mbar_expect_tx(&full[b ^ 1], kTileBytes);
+            tc::tma_load_2d(base + (b ^ 1) * kTileBytes, &tm, &full[b ^ 1], (tn % tiles_x) * kTX,
+                            (tn / tiles_x) * kTY);
+        }
+        tc::mbar_wait(&full[b], (phases >> b) & 1u);
+        phases ^= 1u << b;
+        tile_march<ORDER>(next, gx, (t % tiles_x) * kTX, (t / tiles_x) * kTY, nx, ny, xcfl, ycfl, nullptr, 0,
+                          nullptr, 0, reinterpret_cast<const float*>(base + b * kTileBytes));
+        __syncthreads();
+        b ^= 1;
+    }
+    if (bc) {
+        const int64_t total = 2 * ((int64_t)gx * R + (int64_t)ny * R);
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + tid; i < total; i += stride)
+            bc_item(next, curr, gx, gy, R, s, i);
+    }
+}
+
 // ---- multi-GPU slab: sweep + BC + halo push in one launch ---------------------
 template <int ORDER>
 __global__ void __launch_bounds__(256)
@@ -226,7 +413,7 @@ sweep_slab(float* __restrict__ next, const float* __restrict__ curr,
            float* __restrict__ up_ghost, float* __restrict__ down_ghost, int gx, int rows,
            float xcfl, float ycfl, float s, int is_top, int is_bottom, int tiles_x, int tiles) {
     constexpr int R = ORDER / 2;
-    __shared__ float smem[(kTX + 2 * R) * (kTY + 2 * R)];
+    __shared__ __align__(16) float smem[tile_pitch<R>() * (kTY + 2 * R)];
     const int nx = gx - 2 * R;
     const int gy = rows + 2 * R;
     if ((int)blockIdx.x >= tiles) {
@@ -261,6 +448,24 @@ sweep_slab(float* __restrict__ next, const float* __restrict__ curr,
                         down_ghost, rows - R, smem);
 }
 
+// fp32 2-D tensor map over a grid (gx x gy, rows contiguous) with a box of one tile + halo
+int make_tile_map(CUtensorMap* out, const float* grid, int gx, int gy, int box_w, int box_h) {
+    typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                      CUtensorMapFloatOOBfill);
+    EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(cme::tensor_map_encoder());
+    if (!fn) return -2;
+    cuuint64_t dims[2] = {(cuuint64_t)gx, (cuuint64_t)gy};
+    cuuint64_t strides[1] = {(cuuint64_t)gx * sizeof(float)};
+    cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)box_h};
+    cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(grid), dims, strides, box,
+                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : -3;
+}
+
 template <int ORDER>
 int launch_step(float* next, const float* curr, int gx, int gy, float xcfl, float ycfl,
                 int variant, int bc, float s, cudaStream_t st) {
@@ -284,8 +489,23 @@ int launch_step(float* next, const float* curr, int gx, int gy, float xcfl, floa
         const int tiles_x = (nx + kTX - 1) / kTX, tiles_y = (ny + kTY - 1) / kTY;
         const int64_t tiles = (int64_t)tiles_x * tiles_y;
         CME_CHECK_ARG(tiles + bc_blocks < INT32_MAX, "cme_heat_step: grid too large");
-        sweep_shared<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
-            next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles, bc, s);
+        static const bool tma_off = getenv("CME_STENCIL_NO_TMA") != nullptr;
+        CUtensorMap tm;
+        if (!tma_off && gx % 4 == 0 && ((uintptr_t)curr & 15) == 0 &&
+            make_tile_map(&tm, curr, gx, gy, tile_pitch<R>(), kTY + 2 * R) == 0) {
+            constexpr int kBytes = tma_smem_bytes<R>();
+            static bool opted = false;      // per instantiation; the attribute is per function
+            if (!opted) {
+                CME_CUDA(cudaFuncSetAttribute(sweep_tma<ORDER>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBytes));
+                opted = true;
+            }
+            const int grid = (int)std::min<int64_t>(tiles, 2 * (int64_t)cme::sm_count());
+            sweep_tma<ORDER><<<grid, 256, kBytes, st>>>(tm, next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles,
+                                                         bc, s);
+        } else {
+            sweep_shared<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
+                next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles, bc, s);
+        }
     }
     CME_LAUNCH_CHECK();
     return 0;
