@@ -348,6 +348,36 @@ sweep_shared(float* __restrict__ next, const float* __restrict__ curr, int gx, i
                         nullptr, 0, smem);
 }
 
+// Border decay of one slab (multi-GPU): side columns of every owned row; the full-width bands
+// only where this slab touches the physical top / bottom border.  Work item t of `total`.
+__device__ __forceinline__ int64_t slab_bc_total(int gx, int rows, int R, int is_top, int is_bottom) {
+    return (int64_t)rows * R * 2 + (is_top ? (int64_t)gx * R : 0) + (is_bottom ? (int64_t)gx * R : 0);
+}
+__device__ __forceinline__ void slab_bc_item(float* __restrict__ next, const float* __restrict__ curr,
+                                             int gx, int rows, int R, int is_top, float s, int64_t t) {
+    const int64_t n_side = (int64_t)rows * R * 2;
+    const int64_t n_band = (int64_t)gx * R;
+    int64_t idx;
+    if (t < n_side) {
+        const int64_t row = t / (2 * R);
+        const int k = (int)(t % (2 * R));
+        const int colg = k < R ? k : gx - 2 * R + k;
+        idx = (int64_t)gx * (row + R) + colg;
+    } else if (is_top && t < n_side + n_band) {
+        idx = t - n_side;
+    } else {
+        const int64_t u = t - n_side - (is_top ? n_band : 0);
+        idx = u + (int64_t)gx * (rows + R);
+    }
+    next[idx] = curr[idx] * s;
+}
+
+struct SlabArgs {
+    float* up_ghost;      // upper neighbour's bottom ghost rows (or null)
+    float* down_ghost;    // lower neighbour's top ghost rows (or null)
+    int slab, is_top, is_bottom;
+};
+
 // ---- variant 2 on TMA: persistent blocks, tiles prefetched by the copy engine -------------
 // ncu on sweep_shared: 60 % of the warp stalls are the global loads of the staging loop, with
 // DRAM at 46 % and the issue slots at 46 %: four resident blocks per SM do not hide it.  Here
@@ -361,7 +391,7 @@ template <int ORDER>
 __global__ void __launch_bounds__(256)
 sweep_tma(const __grid_constant__ CUtensorMap tm, float* __restrict__ next,
           const float* __restrict__ curr, int gx, int gy, float xcfl, float ycfl, int tiles_x,
-          int tiles, int bc, float s) {
+          int tiles, int bc, float s, SlabArgs sa) {
     constexpr int R = ORDER / 2;
     constexpr int W = tile_pitch<R>(), HT = kTY + 2 * R;
     constexpr uint32_t kTileBytes = W * HT * 4;
@@ -393,14 +423,20 @@ sweep_tma(const __grid_constant__ CUtensorMap tm, float* __restrict__ next,
         }
         tc::mbar_wait(&full[b], (phases >> b) & 1u);
         phases ^= 1u << b;
-        tile_march<ORDER>(next, gx, (t % tiles_x) * kTX, (t / tiles_x) * kTY, nx, ny, xcfl, ycfl, nullptr, 0,
-                          nullptr, 0, reinterpret_cast<const float*>(base + b * kTileBytes));
+        // slab mode: my first R rows also go to the upper neighbour's bottom ghost rows, my last R
+        // rows to the lower neighbour's top ghost rows
+        tile_march<ORDER>(next, gx, (t % tiles_x) * kTX, (t / tiles_x) * kTY, nx, ny, xcfl, ycfl, sa.up_ghost, R,
+                          sa.down_ghost, ny - R, reinterpret_cast<const float*>(base + b * kTileBytes));
         __syncthreads();
         b ^= 1;
     }
-    if (bc) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (sa.slab) {
+        const int64_t total = slab_bc_total(gx, ny, R, sa.is_top, sa.is_bottom);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + tid; i < total; i += stride)
+            slab_bc_item(next, curr, gx, ny, R, sa.is_top, s, i);
+    } else if (bc) {
         const int64_t total = 2 * ((int64_t)gx * R + (int64_t)ny * R);
-        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
         for (int64_t i = (int64_t)blockIdx.x * blockDim.x + tid; i < total; i += stride)
             bc_item(next, curr, gx, gy, R, s, i);
     }
@@ -417,28 +453,10 @@ sweep_slab(float* __restrict__ next, const float* __restrict__ curr,
     const int nx = gx - 2 * R;
     const int gy = rows + 2 * R;
     if ((int)blockIdx.x >= tiles) {
-        // border decay: side columns of every owned row; the full-width bands
-        // only where this slab touches the physical top / bottom border
-        const int64_t n_side = (int64_t)rows * R * 2;
-        const int64_t n_band = (int64_t)gx * R;
-        const int64_t total = n_side + (is_top ? n_band : 0) + (is_bottom ? n_band : 0);
+        const int64_t total = slab_bc_total(gx, rows, R, is_top, is_bottom);
         const int64_t stride = (int64_t)(gridDim.x - tiles) * blockDim.x;
-        for (int64_t t = (int64_t)(blockIdx.x - tiles) * blockDim.x + threadIdx.x; t < total;
-             t += stride) {
-            int64_t idx;
-            if (t < n_side) {
-                const int64_t row = t / (2 * R);
-                const int k = (int)(t % (2 * R));
-                const int colg = k < R ? k : gx - 2 * R + k;
-                idx = (int64_t)gx * (row + R) + colg;
-            } else if (is_top && t < n_side + n_band) {
-                idx = t - n_side;
-            } else {
-                const int64_t u = t - n_side - (is_top ? n_band : 0);
-                idx = u + (int64_t)gx * (gy - R);
-            }
-            next[idx] = curr[idx] * s;
-        }
+        for (int64_t t = (int64_t)(blockIdx.x - tiles) * blockDim.x + threadIdx.x; t < total; t += stride)
+            slab_bc_item(next, curr, gx, rows, R, is_top, s, t);
         return;
     }
     const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
@@ -464,6 +482,20 @@ int make_tile_map(CUtensorMap* out, const float* grid, int gx, int gy, int box_w
                           estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+// the TMA kernel needs more dynamic shared memory than the default limit (set per device)
+template <int ORDER>
+int opt_in_tma() {
+    static bool done[64] = {};
+    int dev = 0;
+    CME_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+        CME_CUDA(cudaFuncSetAttribute(sweep_tma<ORDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      tma_smem_bytes<ORDER / 2>()));
+        if (dev >= 0 && dev < 64) done[dev] = true;
+    }
+    return 0;
 }
 
 template <int ORDER>
@@ -494,14 +526,10 @@ int launch_step(float* next, const float* curr, int gx, int gy, float xcfl, floa
         if (!tma_off && gx % 4 == 0 && ((uintptr_t)curr & 15) == 0 &&
             make_tile_map(&tm, curr, gx, gy, tile_pitch<R>(), kTY + 2 * R) == 0) {
             constexpr int kBytes = tma_smem_bytes<R>();
-            static bool opted = false;      // per instantiation; the attribute is per function
-            if (!opted) {
-                CME_CUDA(cudaFuncSetAttribute(sweep_tma<ORDER>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBytes));
-                opted = true;
-            }
+            if (int rc = opt_in_tma<ORDER>()) return rc;
             const int grid = (int)std::min<int64_t>(tiles, 2 * (int64_t)cme::sm_count());
             sweep_tma<ORDER><<<grid, 256, kBytes, st>>>(tm, next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles,
-                                                         bc, s);
+                                                         bc, s, SlabArgs{nullptr, nullptr, 0, 0, 0});
         } else {
             sweep_shared<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
                 next, curr, gx, gy, xcfl, ycfl, tiles_x, (int)tiles, bc, s);
@@ -520,8 +548,19 @@ int launch_slab(float* next, const float* curr, float* up, float* down, int gx, 
     const int64_t tiles = (int64_t)tiles_x * tiles_y;
     const int bc_blocks = 2 * cme::sm_count();
     CME_CHECK_ARG(tiles + bc_blocks < INT32_MAX, "cme_heat_slab_step: grid too large");
-    sweep_slab<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
-        next, curr, up, down, gx, rows, xcfl, ycfl, s, is_top, is_bottom, tiles_x, (int)tiles);
+    static const bool tma_off = getenv("CME_STENCIL_NO_TMA") != nullptr;
+    CUtensorMap tm;
+    if (!tma_off && gx % 4 == 0 && ((uintptr_t)curr & 15) == 0 &&
+        make_tile_map(&tm, curr, gx, rows + 2 * R, tile_pitch<R>(), kTY + 2 * R) == 0) {
+        if (int rc = opt_in_tma<ORDER>()) return rc;
+        const int grid = (int)std::min<int64_t>(tiles, 2 * (int64_t)cme::sm_count());
+        sweep_tma<ORDER><<<grid, 256, tma_smem_bytes<R>(), st>>>(tm, next, curr, gx, rows + 2 * R, xcfl, ycfl,
+                                                                 tiles_x, (int)tiles, 1, s,
+                                                                 SlabArgs{up, down, 1, is_top, is_bottom});
+    } else {
+        sweep_slab<ORDER><<<(unsigned)(tiles + bc_blocks), 256, 0, st>>>(
+            next, curr, up, down, gx, rows, xcfl, ycfl, s, is_top, is_bottom, tiles_x, (int)tiles);
+    }
     CME_LAUNCH_CHECK();
     return 0;
 }
