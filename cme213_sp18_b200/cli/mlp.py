@@ -52,6 +52,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--pixel-max", type=int, default=255)
     ap.add_argument("--outdir", default="Outputs")
     ap.add_argument("--device", default=None, help="cpu forces the gloo/CPU schedule")
+    ap.add_argument("--trace", default=None, help="write a Chrome-trace file of the run's phases here "
+                                                  "(rank r writes <file>.r for r > 0)")
     ap.add_argument("--resume", default=None, help="checkpoint to start the parallel run from")
     ap.add_argument("--save-checkpoint", default=None, help="write the trained weights here")
     return ap
@@ -91,11 +93,21 @@ def main(argv=None) -> int:
         print(f"Size of x_train, N =  {x.shape[0]}")
         print(f"Size of label_train = {lab.shape[0]}")
         (x_train, l_train), (x_dev, l_dev) = M.split_train_dev(x, lab)
+    tracer = None
+    if args.trace:
+        from ..utils.tracing import Tracer
+
+        tracer = Tracer(rank=info.rank, device=info.device.type)
+    cpu_tracer = None
+    if args.trace and rank0:
+        from ..utils.tracing import Tracer
+
+        cpu_tracer = Tracer(rank=info.rank, device="cpu")      # the serial trainer runs on the host
     if rank0 and args.run_seq:
         print("Start Sequential Training")
         t0 = time.perf_counter()
         M.train(seq_nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
-                args.print_every, args.debug, outdir=str(out / "CPUmats"))
+                args.print_every, args.debug, outdir=str(out / "CPUmats"), tracer=cpu_tracer)
         print(f"Time for Sequential Training: {time.perf_counter() - t0} seconds")
         prec = M.precision(M.predict(seq_nn, x_dev), l_dev)
         print(f"Precision on validation set for sequential training = {prec}")
@@ -119,10 +131,13 @@ def main(argv=None) -> int:
         box = [x_train, l_train]
         dist.broadcast_object_list(box, src=0)
         x_train, l_train = box
-    parallel_train(nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
-                   args.print_every, args.debug, info=info, precision=precision, comm=args.comm,
-                   data_mode=args.data_mode if precision == "bf16" or args.data_mode != "stream" else "owner",
-                   debug_log=dl)
+    from contextlib import nullcontext
+
+    with (tracer.span("parallel_train", precision=precision, world=info.world) if tracer else nullcontext()):
+        parallel_train(nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
+                       args.print_every, args.debug, info=info, precision=precision, comm=args.comm,
+                       data_mode=args.data_mode if precision == "bf16" or args.data_mode != "stream" else "owner",
+                       debug_log=dl)
     if rank0:
         print(f"Time for Parallel Training: {time.perf_counter() - t0} seconds")
         prec = M.precision(M.predict(nn, x_dev), l_dev)
@@ -132,6 +147,18 @@ def main(argv=None) -> int:
             from ..utils.checkpoint import save_checkpoint
 
             save_checkpoint(args.save_checkpoint, nn, epoch=args.epochs)
+    if tracer is not None:
+        import json
+
+        path = args.trace if info.rank == 0 else f"{args.trace}.{info.rank}"
+        tracer.export_chrome_trace(path)
+        if cpu_tracer is not None and cpu_tracer.spans_ms():
+            # the serial trainer's host spans go into rank 0's file on a row of their own
+            doc = json.loads(open(path).read())
+            for name, start, dur, a in cpu_tracer.spans_ms():
+                doc["traceEvents"].append({"name": name, "ph": "X", "pid": info.rank, "tid": 1, "ts": start * 1e3,
+                                           "dur": dur * 1e3, "args": a})
+            open(path, "w").write(json.dumps(doc))
     rc = 0
     if (args.grade or args.debug) and rank0:
         if dl:

@@ -196,7 +196,7 @@ def print_flag_for(batch: int, it: int, print_every: int) -> bool:
 def train(nn: NeuralNetwork, X: torch.Tensor, labels: torch.Tensor, learning_rate: float = 0.001,
           reg: float = 0.0, epochs: int = 1, batch_size: int = 800, grad_check: bool = False,
           print_every: int = -1, debug: bool = False, outdir: str = "Outputs/CPUmats",
-          log=print) -> dict:
+          log=print, tracer=None) -> dict:
     """Serial fp64 trainer (ref fpcode/neural_network.cpp:219-279): epochs x batches, the last
     batch may be short, plain SGD.  Returns {'iterations', 'losses'}."""
     N = X.shape[0]
@@ -206,7 +206,9 @@ def train(nn: NeuralNetwork, X: torch.Tensor, labels: torch.Tensor, learning_rat
     it = 0
     losses = []
     num_batches = (N + batch_size - 1) // batch_size
-    for _epoch in range(epochs):
+
+    def one_epoch(epoch: int) -> None:
+        nonlocal it
         for batch in range(num_batches):
             lo = batch * batch_size
             hi = min(N, lo + batch_size)
@@ -218,13 +220,20 @@ def train(nn: NeuralNetwork, X: torch.Tensor, labels: torch.Tensor, learning_rat
                     log(f"Gradient check at iteration {it}: {'passed' if ok else 'FAILED'}")
                 val = loss(nn, cache.yc, y[lo:hi], reg)
                 losses.append((it, val))
-                log(f"Loss at iteration {it} of epoch {_epoch}/{epochs} = {val}")
+                log(f"Loss at iteration {it} of epoch {epoch}/{epochs} = {val}")
             for i in range(nn.num_layers):
                 nn.W[i] -= learning_rate * grads.dW[i]
                 nn.b[i] -= learning_rate * grads.db[i]
             if debug and print_flag_for(batch, it, print_every):
                 write_cpudata_tofile(nn, it, outdir)
             it += 1
+
+    for epoch in range(epochs):
+        if tracer is None:
+            one_epoch(epoch)
+        else:
+            with tracer.span("serial epoch", epoch=epoch):
+                one_epoch(epoch)
     return {"iterations": it, "losses": losses}
 
 

@@ -59,3 +59,29 @@ def test_sim_params_file_roundtrip(tmp_path):
     assert SimParams.from_file(tmp_path / "p2.in") == p
     with pytest.raises(ValueError):
         SimParams(order=3)
+
+
+def test_tracer_and_cli_trace_file(tmp_path):
+    """Span tracer (CPU clock here, CUDA events on a GPU) and the mlp CLI's --trace output."""
+    import json
+    import time
+
+    from cme213_sp18_b200.utils.tracing import Tracer
+
+    tr = Tracer(rank=3, device="cpu")
+    with tr.span("outer", step=1):
+        with tr.span("inner"):
+            time.sleep(0.01)
+    tot = tr.totals_ms()
+    assert tot["outer"] >= tot["inner"] >= 9.0
+    doc = json.loads(tr.export_chrome_trace(tmp_path / "t.json").read_text())
+    ev = [e for e in doc["traceEvents"] if e["ph"] == "X"]
+    assert {e["name"] for e in ev} == {"outer", "inner"} and all(e["pid"] == 3 for e in ev)
+    assert Tracer(enabled=False, device="cpu").totals_ms() == {}
+
+    r = run_module("cme213_sp18_b200.cli.mlp", "-n", "16", "-e", "2", "-b", "100", "-s", "--device", "cpu",
+                   "--train-size", "400", "--test-size", "20", "--data-dir", tmp_path / "none",
+                   "--outdir", tmp_path / "Outputs", "--trace", tmp_path / "run.json", cwd=tmp_path)
+    assert r.returncode == 0, r.stdout + r.stderr
+    names = [e["name"] for e in json.loads((tmp_path / "run.json").read_text())["traceEvents"]]
+    assert names.count("serial epoch") == 2 and "parallel_train" in names
