@@ -16,14 +16,22 @@ from ..ops import host
 from .dist import DistInfo, SymmetricTensor
 
 
+def edge_balanced_cuts(row_ptr: np.ndarray, world: int) -> list[int]:
+    """Row boundaries [c_0 = 0, c_1, ..., c_world = N]: rank r owns rows [c_r, c_r+1) and the
+    blocks hold (nearly) equal numbers of edges; row_ptr is the CSR offset array of N + 1 entries."""
+    n = len(row_ptr) - 1
+    m = int(row_ptr[-1])
+    cuts = [int(np.searchsorted(row_ptr, m * r // world)) for r in range(world)] + [n]
+    cuts[0] = 0
+    return cuts
+
+
 class PageRankShards:
     def __init__(self, num_nodes: int, avg_edges: int, info: DistInfo, seed: int = 1):
         self.n, self.avg, self.info = num_nodes, avg_edges, info
         row_ptr, _, inv_deg = host.pagerank_graph(num_nodes, avg_edges, seed, with_edges=False)
         m = int(row_ptr[-1])
-        # equal-edge row partition
-        cuts = [int(np.searchsorted(row_ptr, m * r // info.world)) for r in range(info.world)] + [num_nodes]
-        cuts[0] = 0
+        cuts = edge_balanced_cuts(row_ptr, info.world)
         self.row_begin, self.row_end = cuts[info.rank], cuts[info.rank + 1]
         e0, e1 = int(row_ptr[self.row_begin]), int(row_ptr[self.row_end])
         d = info.device
