@@ -63,6 +63,7 @@ _DEV_SIGS = {
     "cme_gemm_bf16": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P],
     "cme_allreduce_sgd": [P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
+    "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_peer_barrier": [P, c_int, c_int, c_int, c_u32, c_int, c_int, P],
     "cme_peer_copy": [P, P, c_size_t, P],
 }

@@ -172,6 +172,13 @@ int slice_bounds(int64_t r_begin, int64_t r_end, int rank, int nranks, int64_t* 
 
 extern "C" {
 
+int cme_update_slice(int64_t range_begin, int64_t range_end, int rank, int nranks, int64_t out[2]) {
+    CME_CHECK_ARG(out && nranks >= 1 && rank >= 0 && rank < nranks, "cme_update_slice: rank %d of %d", rank, nranks);
+    CME_CHECK_ARG(0 <= range_begin && range_begin <= range_end && range_begin % 4 == 0 && range_end % 4 == 0,
+                  "cme_update_slice: bad range [%lld, %lld)", (long long)range_begin, (long long)range_end);
+    return slice_bounds(range_begin, range_end, rank, nranks, &out[0], &out[1]);
+}
+
 int cme_allreduce_sgd(float* const* grads_host, float* const* params_host, void* const* w1c_host,
                       int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
                       int64_t w2_begin, int64_t w2_end, float lr, float reg, int64_t range_begin,

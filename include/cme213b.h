@@ -251,6 +251,9 @@ int cme_allreduce_sgd(float* const* grads, float* const* params, void* const* w1
                       int nranks, int64_t n_total, int64_t n_w1, int ldx, int kreg,
                       int64_t w2_begin, int64_t w2_end, float lr, float reg, int64_t range_begin,
                       int64_t range_end, void* stream);
+/* The slice [out[0], out[1]) of the update range [range_begin, range_end) that `rank` owns (sums,
+ * updates, and keeps the fp32 master of): whole 16-byte vectors, contiguous, in rank order. */
+int cme_update_slice(int64_t range_begin, int64_t range_end, int rank, int nranks, int64_t out[2]);
 /* Same update through the NVSwitch multicast mapping: multimem.ld_reduce sums in
  * the switch, multimem.st replicates the result to all GPUs. */
 int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_params,

@@ -106,3 +106,28 @@ def test_plan_struct_layout_matches_the_python_mirror():
     for field, _ in _Plan._fields_:
         assert f'"{field}"' in src, f"make_mlp_plan lacks field {field}"
     assert C.sizeof(_Plan) == 6 * 4 + 2 * 4 + 8 + 3 * 16 * 8 + 8 * 8 + 8 + 2 * 4 + 3 * 8
+
+
+def test_master_shard_bounds_agree_between_python_and_c():
+    """MLPEngineBF16.gather_master recomputes which slice of every update range this rank owns;
+    it must be the slice the update kernel's launcher cuts (cme_update_slice), for every bucket."""
+    import random
+
+    lib = _lib.device_lib()
+    rng = random.Random(7)
+    out = (C.c_int64 * 2)()
+    for _ in range(500):
+        world = rng.choice([1, 2, 3, 4, 8])
+        r0 = 4 * rng.randrange(0, 1 << 20)
+        r1 = r0 + 4 * rng.randrange(0, 1 << 22)
+        covered = r0
+        for rank in range(world):
+            assert lib.cme_update_slice(r0, r1, rank, world, out) == 0
+            quads = (r1 - r0) // 4
+            b = r0 + quads * rank // world * 4          # the expressions used in gather_master
+            e = r0 + quads * (rank + 1) // world * 4
+            assert (out[0], out[1]) == (b, e)
+            assert out[0] == covered and out[0] % 4 == 0
+            covered = out[1]
+        assert covered == r1
+    assert lib.cme_update_slice(2, 10, 0, 1, out) == -1      # ranges are whole 16-byte vectors
