@@ -18,6 +18,17 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+def flat_layout(D: int, H: int, C: int) -> dict:
+    """Offsets of the flat fp32 parameter / gradient vector [W1aug (Hp x ldx) | W2 (C x H) | b2 (C)],
+    every segment padded to 4 floats; the C side computes the same (cme_mlp_layout)."""
+    K = D + 1
+    ldx, Hp = _round_up(K, 64), _round_up(H, 64)
+    n_w1 = Hp * ldx
+    o_b2 = n_w1 + _round_up(C * H, 4)
+    return {"K": K, "ldx": ldx, "Hp": Hp, "ldh": Hp, "n_w1": n_w1, "o_w2": n_w1, "o_b2": o_b2,
+            "n_total": o_b2 + _round_up(C, 4)}
+
+
 class MLPEngineBF16:
     """bf16 operands / fp32 accumulate on tcgen05, fp32 master weights.
 
@@ -36,17 +47,12 @@ class MLPEngineBF16:
         self.D, self.Hh, self.C = H
         if self.C != 10:
             raise ValueError("the bf16 engine is built for 10 classes")
-        self.K = self.D + 1                       # pixels + the ones column that carries b1
-        self.ldx = _round_up(self.K, 64)
-        self.Hp = _round_up(self.Hh, 64)
-        self.ldh = self.Hp
+        lay = flat_layout(self.D, self.Hh, self.C)
+        self.K = lay["K"]                         # pixels + the ones column that carries b1
+        self.ldx, self.Hp, self.ldh = lay["ldx"], lay["Hp"], lay["ldh"]
         self.max_rows = max_rows
         self.comm = ("nccl" if comm == "nccl" else "fused") if self.info.world > 1 else "local"
-        r4 = lambda v: _round_up(v, 4)            # noqa: E731
-        self.n_w1 = self.Hp * self.ldx
-        self.o_w2 = self.n_w1
-        self.o_b2 = self.o_w2 + r4(self.C * self.Hh)
-        self.n_total = self.o_b2 + r4(self.C)
+        self.n_w1, self.o_w2, self.o_b2, self.n_total = lay["n_w1"], lay["o_w2"], lay["o_b2"], lay["n_total"]
         d = self.info.device
         self.params = SymmetricTensor(self.n_total, torch.float32, self.info)
         self.grads = SymmetricTensor(self.n_total, torch.float32, self.info)

@@ -68,6 +68,15 @@ int reduce_range(const CmeMlpPlan* p, const Geometry& g, float lr, float reg, in
 
 extern "C" {
 
+int cme_mlp_layout(const CmeMlpPlan* p, int64_t out[4]) {
+    CME_CHECK_ARG(p && out && p->D > 0 && p->H > 0 && p->C > 0, "cme_mlp_layout: bad plan");
+    CME_CHECK_ARG(p->ldx >= p->D + 1 && p->ldx % 64 == 0 && p->Hp >= p->H && p->Hp % 64 == 0 && p->ldh >= p->Hp,
+                  "cme_mlp_layout: ldx=%d Hp=%d ldh=%d do not fit D=%d H=%d", p->ldx, p->Hp, p->ldh, p->D, p->H);
+    const Geometry g = geometry(p);
+    out[0] = g.n_w1, out[1] = g.o_w2, out[2] = g.o_b2, out[3] = g.n_total;
+    return 0;
+}
+
 int cme_mlp_split_point(const CmeMlpPlan* p) {
     if (!p || !p->overlap || p->nranks <= 1) return 0;
     const int hs = (p->H / 2 + 255) / 256 * 256;

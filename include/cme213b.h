@@ -304,6 +304,10 @@ int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* lab
 int cme_mlp_step_ex(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels,
                     int64_t rows, float lr, float reg, float scale, float* loss_sum, void* stream,
                     void* side_stream, void* const* events);
+/* out = {n_w1, o_w2, o_b2, n_total}: float offsets of the flat parameter / gradient vector the
+ * step reads (W1aug at 0, W2 at o_w2, b2 at o_b2, n_total floats in all); rejects a plan whose
+ * leading dimensions do not fit its sizes. */
+int cme_mlp_layout(const CmeMlpPlan* plan, int64_t out[4]);
 /* First hidden unit of the second bucket (0 = the step is not split). */
 int cme_mlp_split_point(const CmeMlpPlan* plan);
 /* Kernels one step launches (memsets not counted). */

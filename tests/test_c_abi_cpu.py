@@ -31,7 +31,7 @@ def test_every_declared_entry_point_is_exported():
 def test_python_signature_table_covers_the_headers():
     # entry points bound outside the table (their ctypes signatures live next to their wrappers)
     bound_elsewhere = {"cme_last_error", "cme_mlp_step", "cme_mlp_step_ex", "cme_mlp_step_launches",
-                       "cme_mlp_split_point", "cme_mlp_runtime_create", "cme_mlp_runtime_run",
+                       "cme_mlp_split_point", "cme_mlp_layout", "cme_mlp_runtime_create", "cme_mlp_runtime_run",
                        "cme_mlp_runtime_stats", "cme_mlp_runtime_destroy", "cme_warmup"}
     declared = _declared("cme213b.h", "cme_")
     missing = declared - set(_lib._DEV_SIGS) - bound_elsewhere
@@ -131,3 +131,27 @@ def test_master_shard_bounds_agree_between_python_and_c():
             covered = out[1]
         assert covered == r1
     assert lib.cme_update_slice(2, 10, 0, 1, out) == -1      # ranges are whole 16-byte vectors
+
+
+def test_flat_vector_layout_agrees_between_python_and_c():
+    """The engine (Python) and the native step (C++) must cut the flat parameter vector at the
+    same offsets for every shape."""
+    import random
+
+    from cme213_sp18_b200.models.mlp_engine import flat_layout
+
+    lib = _lib.device_lib()
+    lib.cme_mlp_layout.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    rng = random.Random(3)
+    out = (C.c_int64 * 4)()
+    shapes = [(784, 100, 10), (784, 1000, 10), (784, 8192, 10), (50, 64, 10)]
+    shapes += [(rng.randrange(1, 2000), rng.randrange(1, 9000), 10) for _ in range(200)]
+    for D, H, Cc in shapes:
+        lay = flat_layout(D, H, Cc)
+        p = _Plan()
+        p.D, p.H, p.C, p.Hp, p.ldx, p.ldh = D, H, Cc, lay["Hp"], lay["ldx"], lay["ldh"]
+        assert lib.cme_mlp_layout(C.addressof(p), out) == 0, _err(lib)
+        assert list(out) == [lay["n_w1"], lay["o_w2"], lay["o_b2"], lay["n_total"]], (D, H, Cc)
+        assert lay["n_total"] % 4 == 0 and lay["o_b2"] % 4 == 0
+    p.ldx -= 64
+    assert lib.cme_mlp_layout(C.addressof(p), out) == -1 and "do not fit" in _err(lib)
