@@ -64,10 +64,21 @@ _DEV_SIGS = {
     "cme_allreduce_sgd": [P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
+    "cme_mlp_dw1_scratch_bytes": [],
+    "cme_mlp_dw1_sync": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int, P, P],
+    "cme_mlp_update_stream": [P, c_float, c_float, P],
+    "cme_mlp_dw1_update": [P, c_i64, c_float, c_float, c_int, P],
+    "cme_mlp_status": [P, P],
+    "cme_mlp_unit_slice": [P, c_int, c_int, P],
+    "cme_mlp_set_step_args": [P, P, P, c_float, c_float, c_float, P],
+    "cme_mlp_step_ex": [P, P, P, c_i64, c_float, c_float, c_float, P, P, P, P],
+    "cme_mlp_step": [P, P, P, c_i64, c_float, c_float, c_float, P, P],
+    "cme_mlp_step_launches": [P],
+    "cme_mlp_layout": [P, P],
     "cme_peer_barrier": [P, c_int, c_int, c_int, c_u32, c_int, c_int, P],
     "cme_peer_copy": [P, P, c_size_t, P],
 }
-_DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t}
+_DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes": c_size_t}
 
 _HOST_SIGS = {
     "cmeh_num_threads": [],

@@ -379,8 +379,15 @@ def peer_copy(src_ptr: int, dst: torch.Tensor, nbytes: int) -> None:
 
 
 # ------------------------------------------------------------------ native step executor
-def make_mlp_plan(eng):
-    """ctypes mirror of CmeMlpPlan (include/cme213b.h) for an MLPEngineBF16."""
+PAD_WORDS = 4096          # csrc/common.cuh kPadWords
+PAD_STATUS = 3106         # kPadStatus
+
+
+def dw1_scratch_words() -> int:
+    return int(device_lib().cme_mlp_dw1_scratch_bytes()) // 4
+
+
+def _plan_type():
     import ctypes as C
 
     class CmeMlpPlan(C.Structure):
@@ -390,9 +397,16 @@ def make_mlp_plan(eng):
                     ("xb", C.c_void_p), ("a1", C.c_void_p), ("dz1", C.c_void_p), ("dz2b", C.c_void_p),
                     ("w2c", C.c_void_p), ("w2t", C.c_void_p), ("dz2", C.c_void_p), ("pred", C.c_void_p),
                     ("pads_dev", C.c_void_p), ("overlap", C.c_int), ("use_mc", C.c_int),
-                    ("grads_mc", C.c_void_p), ("params_mc", C.c_void_p), ("w1c_mc", C.c_void_p)]
+                    ("grads_mc", C.c_void_p), ("params_mc", C.c_void_p), ("w1c_mc", C.c_void_p),
+                    ("unit_rows", C.c_int), ("timeout_ms", C.c_int), ("pad_local", C.c_void_p),
+                    ("sync_scratch", C.c_void_p), ("step_args", C.c_void_p)]
 
-    p = CmeMlpPlan()
+    return CmeMlpPlan
+
+
+def make_mlp_plan(eng):
+    """ctypes mirror of CmeMlpPlan (include/cme213b.h) for an MLPEngineBF16."""
+    p = _plan_type()()
     p.D, p.H, p.C, p.Hp, p.ldx, p.ldh = eng.D, eng.Hh, eng.C, eng.Hp, eng.ldx, eng.ldh
     p.rank, p.nranks, p.max_rows = eng.info.rank, eng.info.world, eng.max_rows
     for r in range(eng.info.world):
@@ -401,29 +415,73 @@ def make_mlp_plan(eng):
         p.w1c[r] = eng.w1c.peer_ptrs[r]
     p.xb, p.a1, p.dz1, p.dz2b = ptr(eng.xb), ptr(eng.a1), ptr(eng.dz1), ptr(eng.dz2b)
     p.w2c, p.w2t, p.dz2, p.pred = ptr(eng.w2c), ptr(eng.w2t), ptr(eng.dz2), ptr(eng.pred)
-    p.pads_dev = ptr(eng.pads_dev) if eng.info.world > 1 else None
-    # same bucketing and reduction flavour as the Python-issued step: the owner of every slice of
-    # the sharded fp32 master depends on it
+    p.pads_dev = ptr(eng.pads_dev)
+    p.pad_local = ptr(eng.pads.tensor)
+    p.sync_scratch = ptr(eng.sync_scratch)
+    p.step_args = ptr(eng.step_args)
+    p.unit_rows, p.timeout_ms = eng.unit_rows, eng.timeout_ms
     p.overlap, p.use_mc = int(eng.overlap), int(eng.use_mc)
     if eng.use_mc:
         p.grads_mc, p.params_mc, p.w1c_mc = eng.grads.multicast_ptr, eng.params.multicast_ptr, eng.w1c.multicast_ptr
     return p
 
 
-def mlp_step_native(plan, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
-                    scale: float, loss_sum: torch.Tensor | None = None) -> None:
-    """The whole step issued by the native executor cme_mlp_step (one C call)."""
+def mlp_step_native(plan, x_u8_ptr: int | None, labels, rows: int, lr: float, reg: float,
+                    scale: float, loss_sum: torch.Tensor | None = None, side_stream=None, events=None) -> None:
+    """The whole step issued by the native executor (one C call).  x_u8_ptr None = the indirect
+    form (inputs, labels, lr, reg, scale from the plan's device-side step arguments).  With a side
+    stream (and 4 events) the update kernel runs next to the dW1 GEMM."""
     import ctypes as C
 
     lib = device_lib()
-    lib.cme_mlp_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
-                                 C.c_float, C.c_void_p, C.c_void_p]
-    lib.cme_mlp_step.restype = C.c_int
-    check(lib.cme_mlp_step(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
-                           stream_ptr()), "cme_mlp_step")
-    lib.cme_mlp_step_launches.argtypes = [C.c_void_p]
-    lib.cme_mlp_step_launches.restype = C.c_int
+    if side_stream is not None:
+        evs = (C.c_void_p * 4)(*[C.c_void_p(int(e.cuda_event)) for e in events])
+        check(lib.cme_mlp_step_ex(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
+                                  stream_ptr(), int(side_stream.cuda_stream), evs), "cme_mlp_step_ex")
+    else:
+        check(lib.cme_mlp_step(C.addressof(plan), x_u8_ptr, ptr(labels), rows, lr, reg, scale, ptr(loss_sum),
+                               stream_ptr()), "cme_mlp_step")
     _count(lib.cme_mlp_step_launches(C.addressof(plan)))
+
+
+def mlp_set_step_args(plan, x_u8_ptr: int, labels, lr: float, reg: float, scale: float) -> None:
+    import ctypes as C
+
+    check(device_lib().cme_mlp_set_step_args(C.addressof(plan), x_u8_ptr, ptr(labels), lr, reg, scale,
+                                             stream_ptr()), "cme_mlp_set_step_args")
+    _count()
+
+
+def mlp_update_stream(plan, lr: float, reg: float) -> None:
+    import ctypes as C
+
+    check(device_lib().cme_mlp_update_stream(C.addressof(plan), lr, reg, stream_ptr()), "cme_mlp_update_stream")
+    _count()
+
+
+def mlp_status(plan) -> int:
+    import ctypes as C
+
+    out = C.c_uint32(0)
+    check(device_lib().cme_mlp_status(C.addressof(plan), C.addressof(out)), "cme_mlp_status")
+    return int(out.value)
+
+
+def mlp_unit_slice(plan, unit: int, rank: int) -> tuple[int, int]:
+    import ctypes as C
+
+    out = (C.c_int64 * 2)()
+    check(device_lib().cme_mlp_unit_slice(C.addressof(plan), unit, rank, out), "cme_mlp_unit_slice")
+    return int(out[0]), int(out[1])
+
+
+def mlp_dw1_sync(dZ1, X, gW1, rows: int, K: int, H: int, ldg: int, scratch, pads_dev, nranks: int,
+                 unit_rows: int, ldh: int | None = None, status_ptr: int | None = None) -> None:
+    check(device_lib().cme_mlp_dw1_sync(ptr(dZ1), ptr(X), ptr(gW1), rows, K, H, X.shape[1],
+                                        ldh if ldh is not None else dZ1.shape[1], ldg, ptr(scratch),
+                                        ptr(pads_dev), nranks, unit_rows, status_ptr, stream_ptr()),
+          "cme_mlp_dw1_sync")
+    _count()
 
 
 def warmup() -> int:

@@ -10,39 +10,22 @@
 // replica.  Flags for ordering between ranks are plain uint32 slots in a
 // peer-mapped pad, bumped with release atomics and polled with acquire loads.
 #include "common.cuh"
+#include "update_stream.cuh"
+
+#include <algorithm>
 
 namespace {
 
-constexpr int kMaxRanks = 16;
+using upd::kMaxRanks;
+using upd::ld_peer_f4;
+using upd::pack2;
+using upd::reg_for;
 
 struct PeerPtrs {
     float* grads[kMaxRanks];
     float* params[kMaxRanks];
     __nv_bfloat16* w1c[kMaxRanks];
 };
-
-__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
-    float4 r;
-    // peer data changes every step: never serve it from a stale L1 line
-    asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-                 : "l"(p)
-                 : "memory");
-    return r;
-}
-__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    return r;
-}
-
-// reg applies to W1 entries (column < kreg of each ldx-long row) and to the W2
-// block [w2_begin, w2_end); biases and pad entries get none
-__device__ __forceinline__ float reg_for(int64_t i, int64_t n_w1, int ldx, int kreg,
-                                         int64_t w2_begin, int64_t w2_end, float reg) {
-    if (i < n_w1) return ((int)(i % ldx) < kreg) ? reg : 0.f;
-    return (i >= w2_begin && i < w2_end) ? reg : 0.f;
-}
 
 __global__ void __launch_bounds__(256)
 allreduce_sgd_p2p_kernel(PeerPtrs pp, int rank, int nranks, int64_t begin, int64_t end,
@@ -160,6 +143,16 @@ peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t 
     for (; i < n16; i += stride) dst[i] = cme::ld_stream_u4(src + i);
 }
 
+// The streaming update as a kernel of its own (plan->overlap == 0, tests): the same code the
+// update warps of the dW1 GEMM run (update_stream.cuh), one CTA per worker group.
+constexpr int kUpdateThreads = 256;
+
+__global__ void __launch_bounds__(kUpdateThreads)
+update_stream_kernel(const __grid_constant__ upd::UpdateArgs a) {
+    __shared__ uint32_t s_ok;
+    upd::run_update(a, blockIdx.x, gridDim.x, threadIdx.x, kUpdateThreads, 1, &s_ok);
+}
+
 int slice_bounds(int64_t r_begin, int64_t r_end, int rank, int nranks, int64_t* b, int64_t* e) {
     // the range [r_begin, r_end) is cut into nranks slices of whole 16-byte vectors
     const int64_t quads = (r_end - r_begin) / 4;
@@ -169,6 +162,45 @@ int slice_bounds(int64_t r_begin, int64_t r_end, int rank, int nranks, int64_t* 
 }
 
 }  // namespace
+
+namespace cme {
+
+int make_update_args(const CmeMlpPlan* p, float lr, float reg, int indirect, upd::UpdateArgs* out) {
+    CME_CHECK_ARG(p && p->pads_dev && p->nranks >= 1 && p->nranks <= upd::kMaxRanks && p->rank >= 0 &&
+                      p->rank < p->nranks, "cme_mlp_update_stream: bad plan");
+    CME_CHECK_ARG(p->unit_rows == 128 || p->unit_rows == 256, "cme_mlp_update_stream: unit_rows %d", p->unit_rows);
+    CME_CHECK_ARG(!(p->use_mc && p->nranks > 1) || (p->grads_mc && p->params_mc && p->w1c_mc),
+                  "cme_mlp_update_stream: use_mc without multicast addresses");
+    CME_CHECK_ARG(!indirect || p->step_args, "cme_mlp_update_stream: indirect arguments need plan->step_args");
+    int64_t lay[4];
+    int rc = cme_mlp_layout(p, lay);
+    if (rc) return rc;
+    upd::UpdateArgs a{};
+    a.enabled = 1;
+    a.use_mc = (p->use_mc && p->nranks > 1) ? 1 : 0;
+    for (int r = 0; r < p->nranks; ++r) {
+        a.grads[r] = p->grads[r];
+        a.params_peer[r] = p->params[r];
+        a.w1c[r] = (__nv_bfloat16*)p->w1c[r];
+        CME_CHECK_ARG(a.grads[r] && a.params_peer[r] && a.w1c[r], "cme_mlp_update_stream: null peer %d", r);
+    }
+    a.mc_grads = p->grads_mc, a.mc_params = p->params_mc, a.mc_w1c = (__nv_bfloat16*)p->w1c_mc;
+    a.pads = p->pads_dev;
+    a.rank = p->rank, a.nranks = p->nranks;
+    a.n_w1 = lay[0], a.n_total = lay[3];
+    a.ldx = p->ldx, a.kreg = p->D;
+    a.w2_begin = lay[1], a.w2_end = lay[1] + (int64_t)p->C * p->H;
+    a.unit_elems = (int64_t)p->unit_rows * p->ldx;
+    a.nunits = (p->Hp + p->unit_rows - 1) / p->unit_rows;
+    CME_CHECK_ARG(a.nunits <= cme::kPadMaxUnits, "cme_mlp_update_stream: %d units", a.nunits);
+    a.lr = lr, a.reg = reg;
+    a.sa = indirect ? p->step_args : nullptr;
+    a.timeout_ns = (unsigned long long)(p->timeout_ms > 0 ? p->timeout_ms : 20000) * 1000000ull;
+    *out = a;
+    return 0;
+}
+
+}  // namespace cme
 
 extern "C" {
 
@@ -228,6 +260,42 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
         mc_grads, local_params, mc_params, (__nv_bfloat16*)mc_w1c, b, e, n_w1, ldx, kreg, w2_begin,
         w2_end, lr, reg);
     CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_update_stream(const CmeMlpPlan* p, float lr, float reg, void* stream) {
+    return cme_mlp_update_stream_ind(p, lr, reg, 0, stream);
+}
+
+namespace {
+__global__ void set_step_args_kernel(CmeStepArgs* dst, CmeStepArgs v) { *dst = v; }
+}  // namespace
+
+int cme_mlp_set_step_args(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* labels, float lr, float reg,
+                          float scale, void* stream) {
+    CME_CHECK_ARG(p && p->step_args && x_u8 && labels, "cme_mlp_set_step_args: the plan has no step_args (or null inputs)");
+    CmeStepArgs v{x_u8, labels, lr, reg, scale, 0};
+    set_step_args_kernel<<<1, 1, 0, cme::as_stream(stream)>>>(p->step_args, v);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_update_stream_ind(const CmeMlpPlan* p, float lr, float reg, int indirect, void* stream) {
+    upd::UpdateArgs a;
+    int rc = cme::make_update_args(p, lr, reg, indirect, &a);
+    if (rc) return rc;
+    // a slice is unit_elems / nranks floats; small CTAs (256 threads, no shared memory), every one
+    // taking its share of every unit
+    const int64_t slice_quads = std::max<int64_t>(1, a.unit_elems / 4 / a.nranks);
+    const int grid = (int)std::min<int64_t>(cme::sm_count(), (slice_quads + kUpdateThreads - 1) / kUpdateThreads);
+    update_stream_kernel<<<grid, kUpdateThreads, 0, cme::as_stream(stream)>>>(a);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_status(const CmeMlpPlan* p, uint32_t* out) {
+    CME_CHECK_ARG(p && out && p->pad_local, "cme_mlp_status: bad argument");
+    CME_CUDA(cudaMemcpy(out, p->pad_local + cme::kPadStatus, sizeof(uint32_t), cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -60,7 +60,45 @@ static inline int stride_grid(int64_t work_items, int block, int blocks_per_sm, 
     return (int)(need < cap ? need : cap);
 }
 
+// ---- flag pad of the MLP step (one pad of kPadWords uint32 per rank, peer-mapped) ----------
+// Words [0, 512) belong to cme_peer_barrier (8 channels x 64).  The streaming update uses:
+//   kPadUnit0 + u   cumulative count of ranks whose gradient unit u is complete (u < kPadMaxUnits;
+//                   kPadTail for the W2/b2 tail), bumped by every rank on every rank's pad
+//   kPadDone0 + r   steps whose update rank r has finished (bumped by r on every pad)
+//   kPadEpoch       local: steps this rank has finished     kPadDoneCtr   local scratch counter
+//   kPadStatus      local: 0, or the code of the wait that timed out (see cme_mlp_status)
+constexpr int kPadWords = 4096;
+constexpr int kPadUnit0 = 2048;
+constexpr int kPadMaxUnits = 1023;
+constexpr int kPadTail = kPadUnit0 + kPadMaxUnits;
+constexpr int kPadDone0 = 3072;
+constexpr int kPadEpoch = 3104;
+constexpr int kPadDoneCtr = 3105;
+constexpr int kPadStatus = 3106;
+
 // ---- device helpers ---------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

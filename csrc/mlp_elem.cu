@@ -31,8 +31,9 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 // ---- staging -------------------------------------------------------------------
 // one thread per 16-element chunk of a destination row
 __global__ void __launch_bounds__(256)
-u8_to_bf16_kernel(const uint8_t* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t rows,
-                  int cols, int ld, int add_ones) {
+u8_to_bf16_kernel(const uint8_t* __restrict__ src_arg, const CmeStepArgs* __restrict__ sa,
+                  __nv_bfloat16* __restrict__ dst, int64_t rows, int cols, int ld, int add_ones) {
+    const uint8_t* __restrict__ src = sa ? sa->x_u8 : src_arg;      // indirect step arguments
     const int chunks = ld / 16;
     const int64_t total = rows * chunks;
     const int64_t gstride = (int64_t)gridDim.x * blockDim.x;
@@ -271,7 +272,12 @@ extern "C" {
 
 int cme_u8_to_bf16_rows(const uint8_t* src, void* dst_bf16, int64_t rows, int cols, int ld,
                         int add_ones, void* stream) {
-    CME_CHECK_ARG(src && dst_bf16 && rows >= 0 && cols > 0, "cme_u8_to_bf16_rows: bad argument");
+    return cme_u8_to_bf16_rows_ind(src, nullptr, dst_bf16, rows, cols, ld, add_ones, stream);
+}
+
+int cme_u8_to_bf16_rows_ind(const uint8_t* src, const CmeStepArgs* step_args, void* dst_bf16, int64_t rows,
+                            int cols, int ld, int add_ones, void* stream) {
+    CME_CHECK_ARG((src || step_args) && dst_bf16 && rows >= 0 && cols > 0, "cme_u8_to_bf16_rows: bad argument");
     CME_CHECK_ARG(ld % 16 == 0 && ld >= cols + (add_ones ? 1 : 0),
                   "cme_u8_to_bf16_rows: ld (%d) must be a multiple of 16 and cover %d columns", ld,
                   cols + (add_ones ? 1 : 0));
@@ -279,7 +285,7 @@ int cme_u8_to_bf16_rows(const uint8_t* src, void* dst_bf16, int64_t rows, int co
     if (rows == 0) return 0;
     const int64_t total = rows * (ld / 16);
     u8_to_bf16_kernel<<<cme::stride_grid(total, 256, 8, 4), 256, 0, cme::as_stream(stream)>>>(
-        src, (__nv_bfloat16*)dst_bf16, rows, cols, ld, add_ones);
+        src, step_args, (__nv_bfloat16*)dst_bf16, rows, cols, ld, add_ones);
     CME_LAUNCH_CHECK();
     return 0;
 }

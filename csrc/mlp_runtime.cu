@@ -8,9 +8,12 @@
 //
 //   copy stream     H2D of step i+1's uint8 pixels + int32 labels from pinned host memory into
 //                   one of two device staging slots
-//   compute stream  one CUDA graph per (slot, rows, lr, reg, scale) holding the whole step
-//                   (cme_mlp_step_ex: staging, forward, backward, fused all-reduce + SGD,
-//                   re-cast; the memset and the first bucket's reduction fork to a side stream)
+//   compute stream  one CUDA graph per distinct row count holding the whole step
+//                   (cme_mlp_step_ex in its indirect form: staging, forward, backward, the
+//                   streaming all-reduce + SGD on a side stream next to the dW1 GEMM, re-cast;
+//                   the staging slot, labels, lr, reg and scale are read from CmeStepArgs in
+//                   device memory, written by a one-thread kernel before each replay, so a
+//                   learning-rate schedule or a long dataset never adds graphs)
 //                   and a one-thread kernel that stores the step's summed cross-entropy
 //                   straight into the caller's pinned (device-mapped) loss array.  A
 //                   cudaMemcpyAsync per step for those 4 bytes was measured at +17 us of host
@@ -46,9 +49,10 @@ struct CmeMlpRuntime {
     cudaEvent_t join_in = nullptr, join_out = nullptr;
     uint8_t* x_stage[2] = {nullptr, nullptr};
     int32_t* y_stage[2] = {nullptr, nullptr};
-    float* loss_dev = nullptr;  // [2]
+    float* loss_dev = nullptr;
     struct LossCursor* cursor = nullptr;  // device: where the next step's loss goes
-    using Key = std::tuple<int, int64_t, float, float, float>;
+    CmeStepArgs* step_args = nullptr;     // owned only if the plan brought none
+    using Key = int64_t;                  // rows
     std::map<Key, cudaGraphExec_t> graphs;
     int64_t h2d_bytes = 0, d2h_bytes = 0, launches = 0, steps = 0;
 };
@@ -71,29 +75,28 @@ __global__ void publish_loss_kernel(LossCursor* c, const float* loss) {
     c->next = i + 1;
 }
 
-int kernels_per_step(const CmeMlpPlan& p) { return cme_mlp_step_launches(&p) + 1; }
+int kernels_per_step(const CmeMlpPlan& p) { return cme_mlp_step_launches(&p) + 2; }   // + set args, publish loss
 
-int issue_step(CmeMlpRuntime* rt, int slot, int64_t rows, float lr, float reg, float scale) {
-    CME_CUDA(cudaMemsetAsync(rt->loss_dev + slot, 0, sizeof(float), rt->compute));
-    const int rc = cme_mlp_step_ex(&rt->plan, rt->x_stage[slot], rt->y_stage[slot], rows, lr, reg, scale,
-                                   rt->loss_dev + slot, rt->compute, rt->side,
-                                   reinterpret_cast<void* const*>(rt->step_ev));
+// the step proper, with its per-step arguments read from rt->plan.step_args on the device
+int issue_step(CmeMlpRuntime* rt, int64_t rows) {
+    CME_CUDA(cudaMemsetAsync(rt->loss_dev, 0, sizeof(float), rt->compute));
+    const int rc = cme_mlp_step_ex(&rt->plan, nullptr, nullptr, rows, 0.f, 0.f, 0.f, rt->loss_dev, rt->compute,
+                                   rt->side, reinterpret_cast<void* const*>(rt->step_ev));
     if (rc) return rc;
-    publish_loss_kernel<<<1, 1, 0, rt->compute>>>(rt->cursor, rt->loss_dev + slot);
+    publish_loss_kernel<<<1, 1, 0, rt->compute>>>(rt->cursor, rt->loss_dev);
     CME_LAUNCH_CHECK();
     return 0;
 }
 
-int graph_for(CmeMlpRuntime* rt, int slot, int64_t rows, float lr, float reg, float scale,
-              cudaGraphExec_t* out) {
-    const CmeMlpRuntime::Key key(slot, rows, lr, reg, scale);
+int graph_for(CmeMlpRuntime* rt, int64_t rows, cudaGraphExec_t* out) {
+    const CmeMlpRuntime::Key key = rows;
     auto it = rt->graphs.find(key);
     if (it != rt->graphs.end()) {
         *out = it->second;
         return 0;
     }
     CME_CUDA(cudaStreamBeginCapture(rt->compute, cudaStreamCaptureModeThreadLocal));
-    const int rc = issue_step(rt, slot, rows, lr, reg, scale);
+    const int rc = issue_step(rt, rows);
     cudaGraph_t g = nullptr;
     const cudaError_t e = cudaStreamEndCapture(rt->compute, &g);
     if (rc != 0) {
@@ -147,6 +150,7 @@ int cme_mlp_runtime_destroy(CmeMlpRuntime* rt) {
     if (rt->join_in) cudaEventDestroy(rt->join_in);
     if (rt->join_out) cudaEventDestroy(rt->join_out);
     if (rt->loss_dev) cudaFree(rt->loss_dev);
+    if (rt->step_args) cudaFree(rt->step_args);
     if (rt->cursor) cudaFree(rt->cursor);
     if (rt->copy) cudaStreamDestroy(rt->copy);
     if (rt->compute) cudaStreamDestroy(rt->compute);
@@ -179,7 +183,11 @@ int cme_mlp_runtime_create(const CmeMlpPlan* plan, int use_graphs, CmeMlpRuntime
         }
         CME_CUDA(cudaEventCreateWithFlags(&rt->join_in, cudaEventDisableTiming));
         CME_CUDA(cudaEventCreateWithFlags(&rt->join_out, cudaEventDisableTiming));
-        CME_CUDA(cudaMalloc(&rt->loss_dev, 2 * sizeof(float)));
+        CME_CUDA(cudaMalloc(&rt->loss_dev, sizeof(float)));
+        if (!rt->plan.step_args) {
+            CME_CUDA(cudaMalloc(&rt->step_args, sizeof(CmeStepArgs)));
+            rt->plan.step_args = rt->step_args;
+        }
         CME_CUDA(cudaMalloc(&rt->cursor, sizeof(LossCursor)));
         return 0;
     };
@@ -220,24 +228,41 @@ int cme_mlp_runtime_run(CmeMlpRuntime* rt, const uint8_t* host_x, const int32_t*
     CME_LAUNCH_CHECK();
     rt->launches += 1;
     for (int s = 0; s < 2; ++s) CME_CUDA(cudaEventRecord(rt->consumed[s], rt->compute));
-    if ((rc = prefetch(rt, 0, host_x, host_labels, row_begin[0], rows[0]))) return rc;
-    for (int i = 0; i < nsteps; ++i) {
-        const int slot = i & 1;
-        if (i + 1 < nsteps)
-            if ((rc = prefetch(rt, slot ^ 1, host_x, host_labels, row_begin[i + 1], rows[i + 1]))) return rc;
-        CME_CUDA(cudaStreamWaitEvent(rt->compute, rt->copied[slot], 0));
-        const float scale = 1.0f / (float)global_rows[i];
-        if (rt->use_graphs) {
-            cudaGraphExec_t exec = nullptr;
-            if ((rc = graph_for(rt, slot, rows[i], lr, reg, scale, &exec))) return rc;
-            CME_CUDA(cudaGraphLaunch(exec, rt->compute));
-        } else {
-            if ((rc = issue_step(rt, slot, rows[i], lr, reg, scale))) return rc;
+    // The loop proper.  Whatever goes wrong inside it, the steps already queued keep reading
+    // host_x / host_labels: the caller's stream (and the copy stream) must still be made to wait
+    // for them before the error is returned, or a caller that frees its arrays races with copies
+    // in flight.
+    auto queue_steps = [&]() -> int {
+        if ((rc = prefetch(rt, 0, host_x, host_labels, row_begin[0], rows[0]))) return rc;
+        for (int i = 0; i < nsteps; ++i) {
+            const int slot = i & 1;
+            if (i + 1 < nsteps)
+                if ((rc = prefetch(rt, slot ^ 1, host_x, host_labels, row_begin[i + 1], rows[i + 1]))) return rc;
+            CME_CUDA(cudaStreamWaitEvent(rt->compute, rt->copied[slot], 0));
+            const float scale = 1.0f / (float)global_rows[i];
+            if ((rc = cme_mlp_set_step_args(&rt->plan, rt->x_stage[slot], rt->y_stage[slot], lr, reg, scale,
+                                            rt->compute))) return rc;
+            if (rt->use_graphs) {
+                cudaGraphExec_t exec = nullptr;
+                if ((rc = graph_for(rt, rows[i], &exec))) return rc;
+                CME_CUDA(cudaGraphLaunch(exec, rt->compute));
+            } else {
+                if ((rc = issue_step(rt, rows[i]))) return rc;
+            }
+            CME_CUDA(cudaEventRecord(rt->consumed[slot], rt->compute));
+            if (loss_host) rt->d2h_bytes += sizeof(float);
+            rt->launches += kernels_per_step(rt->plan);
+            rt->steps += 1;
         }
-        CME_CUDA(cudaEventRecord(rt->consumed[slot], rt->compute));
-        if (loss_host) rt->d2h_bytes += sizeof(float);
-        rt->launches += kernels_per_step(rt->plan);
-        rt->steps += 1;
+        return 0;
+    };
+    const int run_rc = queue_steps();
+    if (run_rc != 0) {
+        // best effort, keeping the first error message: drain what was queued
+        cudaStreamSynchronize(rt->copy);
+        cudaStreamSynchronize(rt->compute);
+        cudaStreamSynchronize(rt->side);
+        return run_rc;
     }
     CME_CUDA(cudaEventRecord(rt->join_out, rt->compute));
     CME_CUDA(cudaStreamWaitEvent(user, rt->join_out, 0));

@@ -4,18 +4,20 @@
 // fpcode/neural_network.cpp:484-541: 6 H2D copies, 13 synchronised launches, 4 D2H copies,
 // 4 host all-reduces, host SGD).  cme_mlp_step is the same unit of work for this library's
 // C/C++ users: given a plan with every device buffer of one rank it issues the whole step
-// (staging, forward, backward, fused all-reduce + SGD, re-cast) with no host synchronisation.
+// (staging, forward, backward, streaming all-reduce + SGD, re-cast) with no host
+// synchronisation.  The Python engine issues its steps through this function too.
 //
-// Schedule (the same one MLPEngineBF16._step_body issues from Python):
-//   side   gradient memset, hidden under staging + the forward GEMM
-//   main   staging, forward GEMM + sigmoid, layer 2 + softmax + CE
-//   main   backward of hidden units [0, hs)           (plan->overlap and more than one rank)
-//   side   barrier, all-reduce + SGD of W1 rows [0, hs), barrier      } concurrently
-//   main   backward of hidden units [hs, H)                           }
-//   main   barrier, all-reduce + SGD of the rest, barrier, join side, re-cast W2
-// Without a side stream the same launches go to the one stream in that order, so the update
-// ranges (and with them the owner of every slice of the sharded fp32 master) never depend on
-// how the step was issued.
+// Schedule:
+//   side   memset of the W2 / b2 gradient tail (a few hundred KB), hidden under staging + forward
+//   main   staging, forward GEMM + sigmoid, layer 2 + softmax + CE, backward tail (dZ1 + dW2)
+//   main   dW1 GEMM + update in ONE kernel: the GEMM publishes every unit (256 rows of W1) of the
+//          gradient as it completes, and four extra warps in each of its CTAs reduce the unit
+//          over NVLink as soon as every rank has published it, apply SGD and replicate the weights
+//   main   re-cast W2
+// Nothing zero-fills the W1 gradient (the first k-chunk of every tile stores), and there are no
+// barrier launches: the flags live inside the kernel.  With plan->overlap == 0 the update runs
+// as a kernel of its own behind the GEMM; the arithmetic and the owner of every slice of the
+// sharded fp32 master are the same either way.
 #include "common.cuh"
 
 namespace {
@@ -35,35 +37,6 @@ Geometry geometry(const CmeMlpPlan* p) {
     return g;
 }
 
-// Backward for hidden units [h0, h0 + hb): dZ1 and its share of dW2 in one pass, then dW1 rows.
-int backward_block(const CmeMlpPlan* p, const Geometry& g, int64_t rows, int h0, int hb, void* stream) {
-    auto* a1 = static_cast<__nv_bfloat16*>(p->a1) + h0;
-    auto* dz1 = static_cast<__nv_bfloat16*>(p->dz1) + h0;
-    auto* w2t = static_cast<__nv_bfloat16*>(p->w2t) + (int64_t)h0 * 64;
-    float* grads = p->grads[p->rank];
-    int rc = cme_mlp_bwd_tail_tc(a1, p->dz2b, w2t, dz1, grads + g.o_w2 + h0, g.H, rows, hb, g.ldh, g.C, stream);
-    if (rc) return rc;
-    return cme_mlp_dw1(dz1, p->xb, grads + (int64_t)h0 * g.ldx, rows, g.K, hb, g.ldx, g.ldh, g.ldx, stream);
-}
-
-// Barrier, fused all-reduce + L2 + SGD + re-cast of [r0, r1) of the flat vector, barrier.
-int reduce_range(const CmeMlpPlan* p, const Geometry& g, float lr, float reg, int64_t r0, int64_t r1,
-                 int channel, void* stream) {
-    int rc;
-    if (p->nranks > 1)
-        if ((rc = cme_peer_barrier(p->pads_dev, p->rank, p->nranks, channel, 0, 1, 1, stream))) return rc;
-    const int64_t w2_end = g.o_w2 + (int64_t)g.C * g.H;
-    if (p->use_mc && p->nranks > 1)
-        rc = cme_allreduce_sgd_mc(p->grads_mc, p->params[p->rank], p->params_mc, p->w1c_mc, p->rank, p->nranks,
-                                  g.n_total, g.n_w1, g.ldx, g.D, g.o_w2, w2_end, lr, reg, r0, r1, stream);
-    else
-        rc = cme_allreduce_sgd(p->grads, p->params, p->w1c, p->rank, p->nranks, g.n_total, g.n_w1, g.ldx,
-                               g.D, g.o_w2, w2_end, lr, reg, r0, r1, stream);
-    if (rc) return rc;
-    if (p->nranks > 1) return cme_peer_barrier(p->pads_dev, p->rank, p->nranks, channel + 1, 0, 1, 1, stream);
-    return 0;
-}
-
 }  // namespace
 
 extern "C" {
@@ -77,21 +50,33 @@ int cme_mlp_layout(const CmeMlpPlan* p, int64_t out[4]) {
     return 0;
 }
 
-int cme_mlp_split_point(const CmeMlpPlan* p) {
-    if (!p || !p->overlap || p->nranks <= 1) return 0;
-    const int hs = (p->H / 2 + 255) / 256 * 256;
-    return (hs > 0 && hs < p->H) ? hs : 0;
+int cme_mlp_unit_slice(const CmeMlpPlan* p, int unit, int rank, int64_t out[2]) {
+    CME_CHECK_ARG(p && out && p->nranks >= 1 && rank >= 0 && rank < p->nranks, "cme_mlp_unit_slice: rank %d", rank);
+    CME_CHECK_ARG(p->unit_rows == 128 || p->unit_rows == 256, "cme_mlp_unit_slice: unit_rows %d", p->unit_rows);
+    const Geometry g = geometry(p);
+    const int nunits = (p->Hp + p->unit_rows - 1) / p->unit_rows;
+    CME_CHECK_ARG(unit >= 0 && unit <= nunits, "cme_mlp_unit_slice: unit %d not in 0..%d", unit, nunits);
+    const int64_t ue = (int64_t)p->unit_rows * p->ldx;
+    const int64_t r0 = unit == nunits ? g.n_w1 : (int64_t)unit * ue;
+    const int64_t r1 = unit == nunits ? g.n_total : ((int64_t)(unit + 1) * ue < g.n_w1 ? (int64_t)(unit + 1) * ue : g.n_w1);
+    const int64_t quads = (r1 - r0) / 4;
+    out[0] = r0 + quads * rank / p->nranks * 4;
+    out[1] = r0 + quads * (rank + 1) / p->nranks * 4;
+    return 0;
 }
 
 int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
                     float lr, float reg, float scale, float* loss_sum, void* stream, void* side_stream,
                     void* const* events) {
-    CME_CHECK_ARG(p && x_u8 && labels, "cme_mlp_step: null argument");
+    CME_CHECK_ARG(p && ((x_u8 && labels) || (!x_u8 && p->step_args)),
+                  "cme_mlp_step: null inputs (and no plan->step_args to read them from)");
+    const CmeStepArgs* sa = x_u8 ? nullptr : p->step_args;
     CME_CHECK_ARG(rows > 0 && rows <= p->max_rows, "cme_mlp_step: rows %lld not in 1..%lld",
                   (long long)rows, (long long)p->max_rows);
     CME_CHECK_ARG(p->nranks >= 1 && p->nranks <= 16 && p->rank >= 0 && p->rank < p->nranks,
                   "cme_mlp_step: rank %d of %d", p->rank, p->nranks);
-    CME_CHECK_ARG(p->nranks == 1 || p->pads_dev, "cme_mlp_step: pads_dev is required with more than one rank");
+    CME_CHECK_ARG(p->pads_dev && p->pad_local && p->sync_scratch,
+                  "cme_mlp_step: the plan needs pads_dev, pad_local and sync_scratch (one rank too)");
     CME_CHECK_ARG(!(p->use_mc && p->nranks > 1) || (p->grads_mc && p->params_mc && p->w1c_mc),
                   "cme_mlp_step: use_mc without multicast addresses");
     CME_CHECK_ARG(!side_stream || events, "cme_mlp_step: a side stream needs 4 events");
@@ -107,30 +92,23 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
         CME_CUDA(cudaEventRecord(ev(0), main_s));
         CME_CUDA(cudaStreamWaitEvent(side_s, ev(0), 0));
     }
-    CME_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * (size_t)g.n_total, side_s));
+    // dW2 and db2 are still accumulated with atomics: zero the tail (W1's gradient is stored)
+    CME_CUDA(cudaMemsetAsync(grads + g.o_w2, 0, sizeof(float) * (size_t)(g.n_total - g.o_w2), side_s));
     if (side_stream) CME_CUDA(cudaEventRecord(ev(1), side_s));
-    if ((rc = cme_u8_to_bf16_rows(x_u8, p->xb, rows, g.D, g.ldx, 1, stream))) return rc;
+    if ((rc = cme_u8_to_bf16_rows_ind(x_u8, sa, p->xb, rows, g.D, g.ldx, 1, stream))) return rc;
     if ((rc = cme_mlp_fwd1(p->xb, p->w1c[p->rank], nullptr, p->a1, rows, g.K, g.H, g.ldx, g.ldh, stream))) return rc;
     if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
-    if ((rc = cme_mlp_fwd2_tc(p->a1, p->w2c, params + g.o_b2, labels, p->dz2, p->dz2b, loss_sum, p->pred,
-                              grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
-
-    const int hs = cme_mlp_split_point(p);
-    if (hs == 0) {
-        if ((rc = backward_block(p, g, rows, 0, g.H, stream))) return rc;
-        if ((rc = reduce_range(p, g, lr, reg, 0, g.n_total, 0, stream))) return rc;
+    if ((rc = cme_mlp_fwd2_tc_ind(p->a1, p->w2c, params + g.o_b2, labels, sa, p->dz2, p->dz2b, loss_sum, p->pred,
+                                  grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
+    if ((rc = cme_mlp_bwd_tail_tc(p->a1, p->dz2b, p->w2t, p->dz1, grads + g.o_w2, g.H, rows, g.H, g.ldh, g.C,
+                                  stream))) return rc;
+    if (p->overlap) {
+        // ONE kernel: the dW1 GEMM with the update warps inside it
+        if ((rc = cme_mlp_dw1_update(p, rows, lr, reg, sa != nullptr, stream))) return rc;
     } else {
-        const int64_t cut = (int64_t)hs * g.ldx;
-        if ((rc = backward_block(p, g, rows, 0, hs, stream))) return rc;
-        if (side_stream) {
-            CME_CUDA(cudaEventRecord(ev(2), main_s));
-            CME_CUDA(cudaStreamWaitEvent(side_s, ev(2), 0));
-        }
-        if ((rc = reduce_range(p, g, lr, reg, 0, cut, 0, side_s))) return rc;
-        if (side_stream) CME_CUDA(cudaEventRecord(ev(3), side_s));
-        if ((rc = backward_block(p, g, rows, hs, g.H - hs, stream))) return rc;
-        if ((rc = reduce_range(p, g, lr, reg, cut, g.n_total, 2, stream))) return rc;
-        if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(3), 0));
+        if ((rc = cme_mlp_dw1_sync(p->dz1, p->xb, grads, rows, g.K, g.H, g.ldx, g.ldh, g.ldx, p->sync_scratch,
+                                   p->pads_dev, p->nranks, p->unit_rows, p->pad_local + cme::kPadStatus, stream))) return rc;
+        if ((rc = cme_mlp_update_stream_ind(p, lr, reg, sa != nullptr, stream))) return rc;
     }
     return cme_mlp_recast_w2(params + g.o_w2, p->w2c, g.ldh, p->w2t, g.H, g.C, stream);
 }
@@ -140,11 +118,44 @@ int cme_mlp_step(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* labels
     return cme_mlp_step_ex(p, x_u8, labels, rows, lr, reg, scale, loss_sum, stream, nullptr, nullptr);
 }
 
-int cme_mlp_step_launches(const CmeMlpPlan* p) {
+int cme_mlp_plan_init_sync(CmeMlpPlan* p) {
+    CME_CHECK_ARG(p && p->nranks == 1 && p->rank == 0, "cme_mlp_plan_init_sync: one-rank plans only "
+                  "(several ranks need peer-mapped pads, see cme213_sp18_b200/parallel/dist.py)");
+    CME_CHECK_ARG(p->Hp > 0 && p->Hp % 64 == 0, "cme_mlp_plan_init_sync: Hp %d", p->Hp);
+    uint32_t* pad = nullptr;
+    uint32_t** table = nullptr;
+    void* scratch = nullptr;
+    CmeStepArgs* sa = nullptr;
+    CME_CUDA(cudaMalloc(&pad, sizeof(uint32_t) * cme::kPadWords));
+    CME_CUDA(cudaMemset(pad, 0, sizeof(uint32_t) * cme::kPadWords));
+    CME_CUDA(cudaMalloc(&table, sizeof(uint32_t*)));
+    CME_CUDA(cudaMemcpy(table, &pad, sizeof(uint32_t*), cudaMemcpyHostToDevice));
+    CME_CUDA(cudaMalloc(&scratch, cme_mlp_dw1_scratch_bytes()));
+    CME_CUDA(cudaMemset(scratch, 0, cme_mlp_dw1_scratch_bytes()));
+    CME_CUDA(cudaMalloc(&sa, sizeof(CmeStepArgs)));
+    CME_CUDA(cudaMemset(sa, 0, sizeof(CmeStepArgs)));
+    p->pad_local = pad;
+    p->pads_dev = table;
+    p->sync_scratch = scratch;
+    p->step_args = sa;
+    p->unit_rows = p->Hp >= 512 ? 256 : 128;
+    p->overlap = 1;
+    return 0;
+}
+
+int cme_mlp_plan_free_sync(CmeMlpPlan* p) {
     if (!p) return 0;
-    const int blocks = cme_mlp_split_point(p) ? 2 : 1;
-    // staging, forward GEMM, layer 2, re-cast + per block: fused tail, dW1, update (+ 2 barriers)
-    return 4 + blocks * (3 + (p->nranks > 1 ? 2 : 0));
+    if (p->pad_local) cudaFree(p->pad_local);
+    if (p->pads_dev) cudaFree((void*)p->pads_dev);
+    if (p->sync_scratch) cudaFree(p->sync_scratch);
+    if (p->step_args) cudaFree(p->step_args);
+    p->pad_local = nullptr, p->pads_dev = nullptr, p->sync_scratch = nullptr, p->step_args = nullptr;
+    return 0;
+}
+
+int cme_mlp_step_launches(const CmeMlpPlan* p) {
+    // staging, forward GEMM, layer 2, backward tail, dW1 (+ update), re-cast
+    return p ? (p->overlap ? 6 : 7) : 0;
 }
 
 }  // extern "C"

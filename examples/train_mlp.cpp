@@ -115,6 +115,7 @@ int main(int argc, char** argv) {
     CK(dev_zeros(&plan.pred, (size_t)batch));
     plan.params[0] = params, plan.grads[0] = grads, plan.w1c[0] = w1c;
     plan.xb = xb, plan.a1 = a1, plan.dz1 = dz1, plan.dz2b = dz2b, plan.w2c = w2c, plan.w2t = w2t;
+    CK(cme_mlp_plan_init_sync(&plan));   // flag pad, split-K counters, device-side step arguments
 
     // weights: 0.01 * N(0,1), biases 0 (ref fpcode/inc/neural_network.h:20-30); b1 lives in
     // column D of the augmented W1, padding stays zero
@@ -158,6 +159,10 @@ int main(int argc, char** argv) {
     std::printf("%.1f k samples/s end to end (first run records the graphs)  h2d %lld B  kernels %lld  graphs %lld\n",
                 (double)samples * epochs / sec / 1e3, (long long)st[0], (long long)st[2], (long long)st[4]);
     CK(cme_mlp_runtime_destroy(rt));
+    uint32_t status = 0;
+    CK(cme_mlp_status(&plan, &status));
+    CK(cme_mlp_plan_free_sync(&plan));
+    if (status != 0) std::fprintf(stderr, "update kernel reported status 0x%x\n", status);
     const bool ok = std::isfinite(last) && last < first;
     std::printf(ok ? "TRAIN_OK\n" : "TRAIN_FAILED\n");
     return ok ? 0 : 1;

@@ -223,12 +223,26 @@ int cme_mlp_recast_w2(const float* W2, void* w2c, int ldh, void* w2t, int H, int
 /* fp32 [rows][ld_src] -> bf16 [rows][ld_dst], first `cols` columns (W2 -> W2c). */
 int cme_f32_to_bf16_2d(const float* src, int ld_src, void* dst_bf16, int ld_dst, int rows, int cols,
                        void* stream);
-/* tcgen05 GEMM #2: gW1[h][k] += sum_r dZ1[r][h] * X[r][k]  (fp32 reductions into
- * gW1, H x K with ld = ldg), both operands MN-major, stream-K balanced over all
- * SMs.  Column K-1 (the ones column) receives the b1 gradient.  Replaces K3
- * (sGEMM_BT_kernel :205-256) for dW1 and K7 for db1.  gW1 must be zeroed first. */
+/* tcgen05 GEMM #2: gW1[h][k] = sum_r dZ1[r][h] * X[r][k]  (H x K fp32 with ld = ldg; every
+ * column below ldg of the rows below H is WRITTEN, the pad columns with zeros), both operands
+ * MN-major, the batch cut into k-chunks dealt to all SMs.  The chunks of a tile are combined in
+ * chunk order (chunk 0 stores, chunk c adds after chunk c-1 has landed), so the result is
+ * bit-reproducible and gW1 needs no zero-fill.  Column K-1 (the ones column) receives the b1
+ * gradient.  Replaces K3 (sGEMM_BT_kernel :205-256) for dW1 and K7 for db1.
+ * cme_mlp_dw1 keeps its chunk counters in a per-device buffer allocated on first use: do not
+ * run two of these calls concurrently on one device.  cme_mlp_dw1_sync takes the counters from
+ * the caller (scratch: cme_mlp_dw1_scratch_bytes() bytes, zeroed once) and, when pads != NULL,
+ * bumps flag kPadUnit0 + u (word 2048 + u) on each of the nranks pads as soon as rows
+ * [u*unit_rows, (u+1)*unit_rows) of gW1 are complete (unit_rows = 128, or 256 for H >= 512):
+ * the publication the streaming update (cme_mlp_update_stream) waits for.  status (may be NULL):
+ * word that receives code 3 if a chunk waits ~2 s for its turn (the grid was not fully resident,
+ * e.g. another large kernel shares the GPU); with NULL the kernel traps instead. */
 int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
                 int ldh, int ldg, void* stream);
+size_t cme_mlp_dw1_scratch_bytes(void);
+int cme_mlp_dw1_sync(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
+                     int ldh, int ldg, void* scratch, uint32_t* const* pads, int nranks, int unit_rows,
+                     uint32_t* status, void* stream);
 
 /* Flat fp32 parameter / gradient vector of the bf16 trainer:
  *   [ W1aug (Hp x ldx, b1 in column K-1) | W2 (C x H) | b2 (C) ]  each segment
@@ -269,6 +283,17 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
  * [max_rows][ldh], dz2 fp32 [max_rows][16], dz2b bf16 [max_rows][64] (zero-initialised),
  * pred int32 [max_rows], w2c bf16 [16][ldh] and w2t bf16 [Hp][64] (zero-initialised).
  * pads_dev: device array of per-rank flag pads (see cme_peer_barrier), NULL for one rank. */
+/* Per-step arguments kept in device memory, so that one recorded CUDA graph serves every
+ * minibatch position and every learning rate: the kernels of a step issued with x_u8 == NULL
+ * read them from plan->step_args; cme_mlp_set_step_args (a one-thread kernel, stream-ordered)
+ * writes them before the step. */
+typedef struct CmeStepArgs {
+    const uint8_t* x_u8;
+    const int32_t* labels;
+    float lr, reg, scale;
+    int reserved;
+} CmeStepArgs;
+
 typedef struct CmeMlpPlan {
     int D, H, C, Hp, ldx, ldh;
     int rank, nranks;
@@ -280,36 +305,84 @@ typedef struct CmeMlpPlan {
     float* dz2;
     int32_t* pred;
     uint32_t* const* pads_dev;
-    /* Optional, zero = off.  overlap: with more than one rank, W1 rows [0, hs) are reduced as a
-     * bucket of their own (on the side stream when one is given) while the rest of the backward
-     * pass runs; hs = cme_mlp_split_point().  The flag also fixes which rank owns which slice of
-     * the sharded fp32 master, so it must not change during a run.  use_mc: reduce through the
-     * NVSwitch multicast mappings below (cme_allreduce_sgd_mc) instead of peer loads. */
+    /* overlap != 0: the streaming update runs on the side stream next to the dW1 GEMM (needs a
+     * side stream); 0: after it, on the same stream (use this under tools that serialise kernels,
+     * e.g. ncu or compute-sanitizer: a kernel that waits for flags cannot start before the kernel
+     * that raises them there).  use_mc: reduce through the NVSwitch multicast mappings below
+     * instead of peer loads. */
     int overlap, use_mc;
     const float* grads_mc;
     float* params_mc;
     void* w1c_mc;
+    /* Streaming update (cme_mlp_update_stream).  unit_rows: rows of W1 per publication unit, 256
+     * when Hp >= 512 else 128; it fixes which rank owns which slice of the sharded fp32 master, so
+     * it must not change during a run.  pad_local = this rank's flag pad (pads_dev[rank], 4096
+     * zero-initialised uint32; required for ONE rank too).  sync_scratch: cme_mlp_dw1_scratch_bytes()
+     * bytes, zeroed once.  timeout_ms: bound on every cross-GPU wait (0 = 20 s). */
+    int unit_rows;
+    int timeout_ms;
+    uint32_t* pad_local;
+    void* sync_scratch;
+    /* Optional: device memory for the indirect step arguments (see CmeStepArgs). */
+    CmeStepArgs* step_args;
 } CmeMlpPlan;
 /* One whole training step on `rows` local samples (uint8 pixels x_u8 [rows][D], labels
  * int32 [rows], both device pointers; x_u8 may be peer-mapped): staging, forward, backward,
- * fused all-reduce + L2 + SGD, bf16 re-cast, with no host synchronisation.
+ * streaming all-reduce + L2 + SGD, bf16 re-cast, with no host synchronisation.
  * scale = 1 / (global samples in the minibatch); loss_sum (may be NULL) += cross-entropy.
  * The C++ counterpart of one iteration of parallel_train's loop
  * (ref fpcode/neural_network.cpp:484-541).  cme_mlp_step issues everything on `stream`;
  * cme_mlp_step_ex also takes a side stream and 4 cudaEvent_t (disable-timing is fine) and
- * moves the gradient memset and the first bucket's reduction there; both are capturable
- * into a CUDA graph from `stream`. */
+ * runs the update kernel there, next to the dW1 GEMM that feeds it; both are capturable
+ * into a CUDA graph from `stream`.  With several ranks every rank must issue the same steps. */
 int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
                  float lr, float reg, float scale, float* loss_sum, void* stream);
+/* x_u8 == NULL selects the indirect form: inputs, labels, lr, reg and scale are read on the
+ * device from plan->step_args (the lr / reg / scale arguments of the call are ignored). */
+int cme_mlp_set_step_args(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, float lr,
+                          float reg, float scale, void* stream);
 int cme_mlp_step_ex(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels,
                     int64_t rows, float lr, float reg, float scale, float* loss_sum, void* stream,
                     void* side_stream, void* const* events);
+/* dW1 GEMM and the update of the step in ONE kernel (the product path): the GEMM's CTAs carry
+ * four extra "update warps" that reduce each unit of the gradient across the GPUs (multimem /
+ * peer loads), apply the SGD step and replicate the new weights as soon as every rank has
+ * published the unit, while the tensor cores work on later units.  Reads plan->dz1 / xb, writes
+ * plan->grads, params, w1c.  indirect != 0: lr / reg from plan->step_args. */
+int cme_mlp_dw1_update(const CmeMlpPlan* plan, int64_t rows, float lr, float reg, int indirect, void* stream);
+/* The update of one step on its own: waits (on the device) for every unit of every rank's
+ * gradient to be published, reduces this rank's slices over NVLink, applies
+ * p -= lr * (g + reg * p), keeps the fp32 master of its slices and stores the bf16 compute copy
+ * of W1 (and the fp32 W2 / b2) into every rank's replica; returns to the stream only when
+ * every rank has written its slices.  Replaces the four MPI_Allreduce calls, the host SGD and
+ * the weight re-upload (ref fpcode/neural_network.cpp:501-541, 486-489). */
+int cme_mlp_update_stream(const CmeMlpPlan* plan, float lr, float reg, void* stream);
+/* The building blocks of a step in their indirect form (step_args != NULL / indirect != 0:
+ * inputs, labels, lr, reg, scale are read from CmeStepArgs in device memory, see above). */
+int cme_mlp_update_stream_ind(const CmeMlpPlan* plan, float lr, float reg, int indirect, void* stream);
+int cme_u8_to_bf16_rows_ind(const uint8_t* src, const CmeStepArgs* step_args, void* dst_bf16, int64_t rows,
+                            int cols, int ld, int add_ones, void* stream);
+int cme_mlp_fwd2_tc_ind(const void* A1, const void* W2c, const float* b2, const int32_t* labels,
+                        const CmeStepArgs* step_args, float* dz2, void* dz2b, float* loss_sum, int32_t* pred,
+                        float* gb2, float scale, int64_t rows, int H, int ldh, int C, void* stream);
+/* *out = 0, or the code of a wait that gave up (low byte 1: a unit of some rank never arrived
+ * within plan->timeout_ms, 2: a rank never finished its update, 3: a k-chunk of the dW1 GEMM
+ * never got its turn; bits 8.. = which).  After a
+ * non-zero status the replicas are not consistent: tear the job down.  Synchronous copy. */
+int cme_mlp_status(const CmeMlpPlan* plan, uint32_t* out);
 /* out = {n_w1, o_w2, o_b2, n_total}: float offsets of the flat parameter / gradient vector the
  * step reads (W1aug at 0, W2 at o_w2, b2 at o_b2, n_total floats in all); rejects a plan whose
  * leading dimensions do not fit its sizes. */
 int cme_mlp_layout(const CmeMlpPlan* plan, int64_t out[4]);
-/* First hidden unit of the second bucket (0 = the step is not split). */
-int cme_mlp_split_point(const CmeMlpPlan* plan);
+/* Float range [out[0], out[1]) of the flat vector whose fp32 master `rank` keeps inside update
+ * unit `unit` (unit == number of W1 units: the W2 / b2 tail). */
+int cme_mlp_unit_slice(const CmeMlpPlan* plan, int unit, int rank, int64_t out[2]);
+/* One-rank convenience for C/C++ callers: allocates (cudaMalloc) and zeroes the flag pad, the
+ * pad pointer table, the split-K counters and the step arguments, and sets unit_rows and
+ * overlap.  Several ranks need peer-mapped pads (cme213_sp18_b200/parallel/dist.py builds them
+ * from symmetric memory). */
+int cme_mlp_plan_init_sync(CmeMlpPlan* plan);
+int cme_mlp_plan_free_sync(CmeMlpPlan* plan);
 /* Kernels one step launches (memsets not counted). */
 int cme_mlp_step_launches(const CmeMlpPlan* plan);
 
@@ -324,7 +397,10 @@ int cme_mlp_step_launches(const CmeMlpPlan* plan);
  * summed cross-entropy of step i is stored by the device into loss_host[i] (pinned and
  * device-mapped, i.e. cudaHostAlloc / cudaHostRegister memory; may be NULL).  Work is ordered
  * after everything already queued on `stream`, and `stream` waits for the last step; the host
- * arrays must stay valid until then.  With several ranks every rank runs the same steps. */
+ * arrays must stay valid until then.  With several ranks every rank runs the same steps.
+ * A non-zero return means a step could not be queued: the call has then waited for everything
+ * it did queue (the host arrays are free again), but with several ranks the peers are left
+ * waiting for this rank's step and give up after plan->timeout_ms: tear all ranks down. */
 typedef struct CmeMlpRuntime CmeMlpRuntime;
 int cme_mlp_runtime_create(const CmeMlpPlan* plan, int use_graphs, CmeMlpRuntime** out);
 int cme_mlp_runtime_run(CmeMlpRuntime* rt, const uint8_t* host_x, const int32_t* host_labels,

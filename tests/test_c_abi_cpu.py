@@ -30,9 +30,11 @@ def test_every_declared_entry_point_is_exported():
 
 def test_python_signature_table_covers_the_headers():
     # entry points bound outside the table (their ctypes signatures live next to their wrappers)
-    bound_elsewhere = {"cme_last_error", "cme_mlp_step", "cme_mlp_step_ex", "cme_mlp_step_launches",
-                       "cme_mlp_split_point", "cme_mlp_layout", "cme_mlp_runtime_create", "cme_mlp_runtime_run",
-                       "cme_mlp_runtime_stats", "cme_mlp_runtime_destroy", "cme_warmup"}
+    bound_elsewhere = {"cme_last_error", "cme_mlp_runtime_create", "cme_mlp_runtime_run",
+                       "cme_mlp_runtime_stats", "cme_mlp_runtime_destroy", "cme_warmup",
+                       # C/C++-only conveniences and the indirect building blocks the native step calls
+                       "cme_mlp_plan_init_sync", "cme_mlp_plan_free_sync", "cme_mlp_update_stream_ind",
+                       "cme_u8_to_bf16_rows_ind", "cme_mlp_fwd2_tc_ind"}
     declared = _declared("cme213b.h", "cme_")
     missing = declared - set(_lib._DEV_SIGS) - bound_elsewhere
     assert not missing, f"no Python binding for {sorted(missing)}"
@@ -67,69 +69,66 @@ def test_bad_arguments_are_rejected_with_a_message():
     assert "null" in _err(lib)
 
 
-class _Plan(C.Structure):
-    _fields_ = [("D", C.c_int), ("H", C.c_int), ("C", C.c_int), ("Hp", C.c_int), ("ldx", C.c_int),
-                ("ldh", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("max_rows", C.c_int64),
-                ("params", C.c_void_p * 16), ("grads", C.c_void_p * 16), ("w1c", C.c_void_p * 16),
-                ("xb", C.c_void_p), ("a1", C.c_void_p), ("dz1", C.c_void_p), ("dz2b", C.c_void_p),
-                ("w2c", C.c_void_p), ("w2t", C.c_void_p), ("dz2", C.c_void_p), ("pred", C.c_void_p),
-                ("pads_dev", C.c_void_p), ("overlap", C.c_int), ("use_mc", C.c_int),
-                ("grads_mc", C.c_void_p), ("params_mc", C.c_void_p), ("w1c_mc", C.c_void_p)]
-
-
-@pytest.mark.parametrize("H,nranks,overlap,expect", [(8192, 8, 1, 4096), (8192, 1, 1, 0), (8192, 8, 0, 0),
-                                                      (1024, 2, 1, 512), (1000, 2, 1, 512), (300, 2, 1, 256),
-                                                      (256, 2, 1, 0), (100, 4, 1, 0)])
-def test_split_point_matches_the_engine_rule(H, nranks, overlap, expect):
-    """cme_mlp_split_point must equal MLPEngineBF16.buckets(): round_up(H / 2, 256) if inside
-    (0, H).  The owner of every slice of the sharded fp32 master depends on it."""
-    lib = _lib.device_lib()
-    lib.cme_mlp_split_point.argtypes = [C.c_void_p]
-    lib.cme_mlp_step_launches.argtypes = [C.c_void_p]
-    p = _Plan()
-    p.D, p.H, p.C, p.nranks, p.overlap = 784, H, 10, nranks, overlap
-    hs = (H // 2 + 255) // 256 * 256
-    rule = hs if (overlap and nranks > 1 and 0 < hs < H) else 0
-    assert rule == expect
-    assert lib.cme_mlp_split_point(C.addressof(p)) == expect
-    blocks = 2 if expect else 1
-    assert lib.cme_mlp_step_launches(C.addressof(p)) == 4 + blocks * (3 + (2 if nranks > 1 else 0))
-
-
-def test_plan_struct_layout_matches_the_python_mirror():
-    """make_mlp_plan builds the same struct: its size must be what the C side reads."""
-    import inspect
-
+def _Plan():
     from cme213_sp18_b200.ops import device as dev
 
-    src = inspect.getsource(dev.make_mlp_plan)
-    for field, _ in _Plan._fields_:
-        assert f'"{field}"' in src, f"make_mlp_plan lacks field {field}"
-    assert C.sizeof(_Plan) == 6 * 4 + 2 * 4 + 8 + 3 * 16 * 8 + 8 * 8 + 8 + 2 * 4 + 3 * 8
+    return dev._plan_type()()
+
+
+def test_plan_struct_layout_matches_the_header():
+    """The ctypes mirror must have the size the C side reads: recompute it from the header's
+    field list (ints, int64, pointers; natural alignment)."""
+    from cme213_sp18_b200.ops import device as dev
+
+    text = (ROOT / "include" / "cme213b.h").read_text()
+    body = text[text.index("typedef struct CmeMlpPlan {"):text.index("} CmeMlpPlan;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split("{", 1)[1].split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        for part in decl.split(","):
+            names.append(re.sub(r"\[.*\]", "", part.strip().split()[-1].lstrip("*")))
+    mirror = [f for f, _ in dev._plan_type()._fields_]
+    assert names == mirror, (names, mirror)
+    # 8 ints, int64, 3 x 16 pointers, 8 pointers, pads_dev, 2 ints, 3 pointers, 2 ints, 3 pointers
+    assert C.sizeof(dev._plan_type()) == 8 * 4 + 8 + 3 * 16 * 8 + 8 * 8 + 8 + 2 * 4 + 3 * 8 + 2 * 4 + 3 * 8
 
 
 def test_master_shard_bounds_agree_between_python_and_c():
-    """MLPEngineBF16.gather_master recomputes which slice of every update range this rank owns;
-    it must be the slice the update kernel's launcher cuts (cme_update_slice), for every bucket."""
+    """cme_mlp_unit_slice names the slice of every update unit whose fp32 master a rank keeps
+    (MLPEngineBF16.gather_master and the update kernel both use this arithmetic): the slices of
+    all ranks must tile every unit exactly, in whole 16-byte vectors."""
     import random
+
+    from cme213_sp18_b200.models.mlp_engine import flat_layout
 
     lib = _lib.device_lib()
     rng = random.Random(7)
     out = (C.c_int64 * 2)()
-    for _ in range(500):
+    for _ in range(200):
         world = rng.choice([1, 2, 3, 4, 8])
-        r0 = 4 * rng.randrange(0, 1 << 20)
-        r1 = r0 + 4 * rng.randrange(0, 1 << 22)
-        covered = r0
-        for rank in range(world):
-            assert lib.cme_update_slice(r0, r1, rank, world, out) == 0
-            quads = (r1 - r0) // 4
-            b = r0 + quads * rank // world * 4          # the expressions used in gather_master
-            e = r0 + quads * (rank + 1) // world * 4
-            assert (out[0], out[1]) == (b, e)
-            assert out[0] == covered and out[0] % 4 == 0
-            covered = out[1]
-        assert covered == r1
+        H = rng.choice([100, 128, 300, 1000, 1024, 8192, rng.randrange(1, 5000)])
+        lay = flat_layout(784, H, 10)
+        p = _Plan()
+        p.D, p.H, p.C, p.Hp, p.ldx, p.ldh, p.nranks = 784, H, 10, lay["Hp"], lay["ldx"], lay["ldh"], world
+        p.unit_rows = 256 if lay["Hp"] >= 512 else 128
+        nunits = (lay["Hp"] + p.unit_rows - 1) // p.unit_rows
+        covered = 0
+        for unit in range(nunits + 1):
+            r0 = lay["n_w1"] if unit == nunits else unit * p.unit_rows * lay["ldx"]
+            r1 = lay["n_total"] if unit == nunits else min((unit + 1) * p.unit_rows * lay["ldx"], lay["n_w1"])
+            assert r0 == covered
+            for rank in range(world):
+                assert lib.cme_mlp_unit_slice(C.addressof(p), unit, rank, out) == 0, _err(lib)
+                quads = (r1 - r0) // 4
+                assert (out[0], out[1]) == (r0 + quads * rank // world * 4, r0 + quads * (rank + 1) // world * 4)
+                assert out[0] == covered and out[0] % 4 == 0
+                covered = out[1]
+            assert covered == r1
+        assert covered == lay["n_total"]
+    assert lib.cme_mlp_unit_slice(C.addressof(p), nunits + 1, 0, out) == -1
     assert lib.cme_update_slice(2, 10, 0, 1, out) == -1      # ranges are whole 16-byte vectors
 
 
@@ -141,7 +140,6 @@ def test_flat_vector_layout_agrees_between_python_and_c():
     from cme213_sp18_b200.models.mlp_engine import flat_layout
 
     lib = _lib.device_lib()
-    lib.cme_mlp_layout.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
     rng = random.Random(3)
     out = (C.c_int64 * 4)()
     shapes = [(784, 100, 10), (784, 1000, 10), (784, 8192, 10), (50, 64, 10)]
