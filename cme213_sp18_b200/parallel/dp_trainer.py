@@ -70,6 +70,19 @@ def parallel_train_cpu(nn, X, labels, lr, reg, epochs, batch_size, info: DistInf
 
 
 # ----------------------------------------------------------------------------- GPU path
+def as_pixels_u8(X: torch.Tensor) -> torch.Tensor:
+    """The device engines train on uint8 pixels (the IDX payload).  A float tensor is accepted
+    only if every value already IS an integer in 0..255; anything else (normalised inputs, say)
+    would silently train on different data than the CPU path, so it is refused."""
+    if X.dtype == torch.uint8:
+        return X
+    r = X.round()
+    if not bool(((r == X) & (X >= 0) & (X <= 255)).all()):
+        raise ValueError("the GPU engines take uint8 pixels (or float tensors holding exact integers in "
+                         "0..255); rescale the inputs, or train on device='cpu' (fp64, any real-valued X)")
+    return r.to(torch.uint8)
+
+
 class DataParallelTrainer:
     """Owns the engine and the device-resident dataset for one rank.
 
@@ -114,10 +127,10 @@ class DataParallelTrainer:
         if D != self.H[0]:
             raise ValueError(f"data has {D} features, the model expects {self.H[0]}")
         if self.data_mode == "owner":
-            self.data = SymmetricTensor(self.N * D, torch.uint8, info, zero=False)
+            self.data = SymmetricTensor(self.N * D + 32, torch.uint8, info, zero=False)
             lab = torch.zeros(self.N, dtype=torch.int32, device=info.device)
             if info.rank == 0:
-                self.data.tensor.copy_(X_u8.reshape(-1).to(info.device, non_blocking=True))
+                self.data.tensor[: self.N * D].copy_(X_u8.reshape(-1).to(info.device, non_blocking=True))
                 lab.copy_(labels.to(info.device, torch.int32))
             dist.broadcast(lab, src=0)     # class ids, once at set-up (ref scattered 10xN one-hot per step)
             self.labels = lab
@@ -159,11 +172,14 @@ class DataParallelTrainer:
                             from ..ops import device as dev
 
                             if fp64_x is None:
-                                fp64_x = torch.empty(self.max_rows * D + 16, dtype=torch.uint8,
+                                fp64_x = torch.empty(self.max_rows * D + 48, dtype=torch.uint8,
                                                      device=info.device)
-                            nbytes = (in_proc * D + 15) // 16 * 16
                             base = self._data_base + lo * D
-                            dev.peer_copy(base - (base % 16), fp64_x, nbytes + 16)
+                            first = base - (base % 16)
+                            # whole 16-byte vectors covering the slice, never past the owner's buffer
+                            # (the symmetric allocation is padded by 32 bytes in set_data)
+                            nbytes = (base + in_proc * D - first + 15) // 16 * 16
+                            dev.peer_copy(first, fp64_x, nbytes)
                             xs = fp64_x[base % 16: base % 16 + in_proc * D].view(in_proc, D)
                         else:
                             xs = src[lo: lo + in_proc]
@@ -185,7 +201,7 @@ class DataParallelTrainer:
                     if debug_log is not None and info.is_main:
                         debug_log.write(nn, it)
                 it += 1
-        eng.store_params(nn)
+        eng.store_params(nn)             # raises if a cross-GPU wait timed out (bf16 engine)
         return {"iterations": it, "losses": losses}
 
 
@@ -194,8 +210,9 @@ def parallel_train(nn, X, labels, learning_rate: float = 0.001, reg: float = 0.0
                    debug: bool = False, info: DistInfo | None = None, precision: str = "bf16",
                    comm: str = "fused", data_mode: str = "owner", debug_log=None, log=print) -> dict:
     """Same call shape as the reference's parallel_train (ref fpcode/inc/neural_network.h:44-47).
-    X: [N, D] uint8 (or float) images, labels: [N] class ids; only rank 0 needs them in "owner"
-    mode.  data_mode="stream" keeps the dataset in pinned host memory and feeds every step
+    X: [N, D] uint8 images (a float tensor must hold exact integers 0..255, see as_pixels_u8; the
+    CPU schedule takes any real-valued X), labels: [N] class ids; only rank 0 needs them in
+    "owner" mode.  data_mode="stream" keeps the dataset in pinned host memory and feeds every step
     through the native runtime (stream_train).  On return `nn` holds the trained weights on
     every rank."""
     del grad_check  # the analytic/numeric check lives in the serial trainer and the tests
@@ -207,7 +224,7 @@ def parallel_train(nn, X, labels, learning_rate: float = 0.001, reg: float = 0.0
     if data_mode == "stream":
         if precision != "bf16" or X is None:
             raise ValueError('data_mode="stream" is the bf16 engine fed from host memory: every rank passes X')
-        Xs = X if X.dtype == torch.uint8 else X.round().clamp(0, 255).to(torch.uint8)
+        Xs = as_pixels_u8(X)
         out = stream_train(nn, Xs, labels, learning_rate, reg, epochs, batch_size, info, comm=comm,
                            print_every=print_every, log=log)
         out["seconds"] = time.perf_counter() - t0
@@ -216,7 +233,7 @@ def parallel_train(nn, X, labels, learning_rate: float = 0.001, reg: float = 0.0
                                   data_mode=data_mode)
     Xu8 = None
     if X is not None:
-        Xu8 = X if X.dtype == torch.uint8 else X.round().clamp(0, 255).to(torch.uint8)
+        Xu8 = as_pixels_u8(X)
     trainer.set_data(Xu8, labels)
     out = trainer.train(nn, learning_rate, reg, epochs, print_every=print_every,
                         debug_log=debug_log if debug else None, log=log, debug=bool(debug))

@@ -198,7 +198,8 @@ int cme_sanitize_compact(const uint8_t* in, size_t n, uint8_t* out, int64_t* out
     }
     CME_CHECK_ARG(in && out && scratch, "cme_sanitize_compact: null buffer");
     const size_t nblocks = (n + kCompactTile - 1) / kCompactTile;
-    CME_CHECK_ARG(nblocks < (1u << 31), "cme_sanitize_compact: input too large");
+    // block counts, scanned offsets and scatter positions are 32-bit
+    CME_CHECK_ARG(n < (1ull << 32), "cme_sanitize_compact: %zu bytes; one call handles fewer than 2^32", n);
     CME_CHECK_ARG(scratch_bytes >= nblocks * sizeof(uint32_t),
                   "cme_sanitize_compact: scratch needs %zu bytes, got %zu",
                   nblocks * sizeof(uint32_t), scratch_bytes);
@@ -289,22 +290,17 @@ static __device__ __align__(256) uint32_t g_noalloc_counts[kNoAllocSlots];    //
 namespace {
 
 // In host code `g_noalloc_counts` is only a handle for the runtime, never an
-// address a kernel may dereference: the device address has to be asked for, per
-// device, with that device current.
-std::mutex g_noalloc_mu;
-uint32_t* g_noalloc_addr[64] = {nullptr};
-
+// address a kernel may dereference: the device address has to be asked for, with
+// the device that will run the kernels current.  It is asked for on EVERY call
+// and never cached: once the library's module is on the device this is a host-side
+// table lookup, and an address remembered across cudaDeviceReset (or any other
+// re-creation of the primary context, which a plug-in cannot prevent its host
+// program from doing) would point into memory that no longer belongs to the array.
 int noalloc_scratch_for_current_device(uint32_t** out) {
-    int dev = 0;
-    CME_CUDA(cudaGetDevice(&dev));
-    CME_CHECK_ARG(dev >= 0 && dev < 64, "cme_sanitize_compact_noalloc: device ordinal %d", dev);
-    std::lock_guard<std::mutex> lk(g_noalloc_mu);
-    if (g_noalloc_addr[dev] == nullptr) {
-        uint32_t* p = nullptr;
-        CME_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_counts));
-        g_noalloc_addr[dev] = p;
-    }
-    *out = g_noalloc_addr[dev];
+    uint32_t* p = nullptr;
+    CME_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_counts));
+    CME_CHECK_ARG(p != nullptr, "cme_sanitize_compact_noalloc: the scratch array has no device address");
+    *out = p;
     return 0;
 }
 

@@ -189,6 +189,8 @@ int make_update_args(const CmeMlpPlan* p, float lr, float reg, int indirect, upd
     a.rank = p->rank, a.nranks = p->nranks;
     a.n_w1 = lay[0], a.n_total = lay[3];
     a.ldx = p->ldx, a.kreg = p->D;
+    CME_CHECK_ARG(lay[3] < (1ll << 31), "cme_mlp_update_stream: %lld parameters; the update indexes with 31 bits", (long long)lay[3]);
+    a.ldx_magic = (uint32_t)(((1ull << 32) + (uint64_t)p->ldx - 1) / (uint64_t)p->ldx);
     a.w2_begin = lay[1], a.w2_end = lay[1] + (int64_t)p->C * p->H;
     a.unit_elems = (int64_t)p->unit_rows * p->ldx;
     a.nunits = (p->Hp + p->unit_rows - 1) / p->unit_rows;

@@ -596,13 +596,15 @@ __device__ __forceinline__ void dw_wait_turn(const DwSync& sy, const uint32_t* c
     if (kc > 0) {
         if (lane == 0) {
             const long long t0 = clock64();
-            while (cme::ld_acquire_gpu(ctr) != (uint32_t)kc) {
+            while (cme::ld_relaxed_gpu(ctr) != (uint32_t)kc) {
                 if (clock64() - t0 > (4ll << 30)) {
                     if (!sy.status) __trap();
                     atomicCAS(sy.status, 0u, 3u | ((uint32_t)kc << 8) | ((uint32_t)(ctr - sy.part_ctr) << 12));
                     break;
                 }
             }
+            // no acquire fence: what follows are reductions performed at L2, which apply in
+            // arrival order behind the stores the previous chunk released before it set the counter
         }
         __syncwarp();
     }
@@ -1578,11 +1580,16 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
     sy.pads = pads;
     sy.status = status;
     sy.nranks = nranks;
-    // B (the minibatch) is re-read once per group of row blocks.  When it stays in L2 anyway, every
-    // row block is its own group, so row blocks complete one after the other while the kernel runs
-    // and the update warps overlap almost all of it; a minibatch that does not fit is walked
-    // in at most 4 groups (4 passes over X from HBM, hidden under a compute-bound kernel).
-    const bool x_in_l2 = (double)rows * ldx * 2.0 <= 32.0e6;
+    // Row blocks are walked in `sblocks` groups; a group's units are complete (and their update
+    // starts) before the next group begins, at the price of one more pass over B (the minibatch)
+    // per group.  Inside a group the k-chunks of a tile are a whole round of items apart, so
+    // nobody waits for its turn, PROVIDED the group holds at least as many tiles as there are
+    // CTAs; a smaller group puts the chunks of one tile on neighbouring CTAs at the same time and
+    // their epilogues queue up behind each other.  That is harmless when a chunk is long (>= 128
+    // k-blocks: 4 groups then, measured 2.02 vs 2.06 ms per step at 65536 rows) and ruinous when
+    // it is short (8192 rows per GPU: 32 k-blocks per chunk, dW1 0.33 instead of 0.12 ms with one
+    // group per row block), so short chunks use a single group: all units then complete during
+    // the last chunk phase, the last quarter of the kernel, in row-block order.
     // CTA-pair path for big problems: 256 x 256 tiles (columns past K are masked in the epilogue)
     static const bool pairs_off = getenv("CME_NO_PAIRS") != nullptr;
     if (!pairs_off && H >= 512 && K >= 256 && kb_total >= 16 && unit_rows == 256) {
@@ -1602,7 +1609,7 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
         sy.parts_per_tile = n2 * 2;
         sy.tiles_per_unit = 1;
         sy.m_tiles = m2;
-        sy.sblocks = x_in_l2 ? m2 : std::min(m2, 4);
+        sy.sblocks = (kb_total / ks >= 128) ? std::min(m2, 4) : 1;
         if ((rc = opt_in_smem(gemm_mnmajor2_kernel, kSmemMNMajor2))) return rc;
         const long long items2 = (long long)m2 * n2 * ks;
         const int pairs = (int)std::min<long long>(items2, npairs);
@@ -1616,9 +1623,10 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
     sy.parts_per_tile = n_tiles;
     sy.tiles_per_unit = unit_rows / BM;
     sy.m_tiles = m_tiles;
-    sy.sblocks = x_in_l2 ? m_tiles : std::min(m_tiles, 4);
+    sy.sblocks = 1;                      // filled in below, once ksplit is known
     if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
     const int ksplit = choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
+    sy.sblocks = (kb_total / ksplit >= 128) ? std::min(m_tiles, 4) : 1;
     const long long items = (long long)m_tiles * n_tiles * ksplit;
     const int grid = (int)std::min<long long>(items, cme::sm_count());
     gemm_mnmajor_kernel<<<grid, threads, kSmemMNMajor, st>>>(

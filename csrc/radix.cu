@@ -168,7 +168,9 @@ int cme_radix_sort(uint32_t* keys, uint32_t* tmp, size_t n, void* scratch, size_
                   "cme_radix_sort: scratch needs %zu bytes, got %zu", cme_radix_scratch_bytes(n),
                   scratch_bytes);
     const size_t nblocks = (n + kTile - 1) / kTile;
-    CME_CHECK_ARG(nblocks < (1u << 22), "cme_radix_sort: too many keys for one call");
+    // histogram offsets and key positions are 32-bit
+    CME_CHECK_ARG(n < (1ull << 32) && nblocks < (1u << 22),
+                  "cme_radix_sort: %zu keys; one call sorts fewer than 2^32 keys", n);
     cudaStream_t st = cme::as_stream(stream);
     uint32_t* histo = (uint32_t*)scratch;
     uint32_t* src = keys;

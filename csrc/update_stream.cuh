@@ -39,6 +39,7 @@ struct UpdateArgs {
     int rank, nranks;
     int64_t n_w1, n_total;
     int ldx, kreg;
+    uint32_t ldx_magic;           // ceil(2^32 / ldx), see sgd4
     int64_t w2_begin, w2_end;
     int64_t unit_elems;
     int nunits;
@@ -71,24 +72,57 @@ __device__ __forceinline__ float reg_for(int64_t i, int64_t n_w1, int ldx, int k
 }
 
 __device__ __forceinline__ bool wait_flag_sys(const uint32_t* p, uint32_t want, unsigned long long timeout_ns) {
-    if ((int32_t)(cme::ld_acquire_sys(p) - want) >= 0) return true;
-    const unsigned long long t0 = cme::global_timer_ns();
-    for (;;) {
+    bool ok = (int32_t)(cme::ld_relaxed_sys(p) - want) >= 0;
+    if (!ok) {
+        const unsigned long long t0 = cme::global_timer_ns();
+        while (!ok) {
 #pragma unroll 1
-        for (int i = 0; i < 32; ++i)
-            if ((int32_t)(cme::ld_acquire_sys(p) - want) >= 0) return true;
-        if (cme::global_timer_ns() - t0 > timeout_ns) return false;
+            for (int i = 0; i < 16 && !ok; ++i) {
+                __nanosleep(64);
+                ok = (int32_t)(cme::ld_relaxed_sys(p) - want) >= 0;
+            }
+            if (!ok && cme::global_timer_ns() - t0 > timeout_ns) return false;
+        }
     }
+    // No acquire fence here, on purpose.  A sys-scope fence costs 3-6 us on this machine while
+    // stores are in flight (ncu: the update's threads spent their time behind thread 0's MEMBAR.SYS),
+    // and nothing it would order can go wrong: the producer made its data visible at system scope
+    // before it bumped the flag (fence + red.release.sys), the flag is observed by a load that
+    // completes before the group's barrier, and every load of the data is issued after that
+    // barrier as a sys-scope / multimem access that is served by the owning GPU's L2, never by a
+    // cache on this side.
+    return true;
 }
 
+// p - lr * (s + reg * p) for one aligned vector of four; rows are ldx (a multiple of 4) long, so
+// the four share a row and ONE column computation serves them.  The column comes from a
+// multiply-high with ldx_magic = ceil(2^32 / ldx) plus a fix-up (the flat vector is < 2^31 long,
+// checked on the host): a 64-bit remainder per element was most of this kernel's instructions.
 __device__ __forceinline__ float4 sgd4(const float4& p, const float4& s, int64_t i, const UpdateArgs& a,
                                        float lr, float reg) {
-    float4 q;
-    q.x = p.x - lr * (s.x + reg_for(i, a.n_w1, a.ldx, a.kreg, a.w2_begin, a.w2_end, reg) * p.x);
-    q.y = p.y - lr * (s.y + reg_for(i + 1, a.n_w1, a.ldx, a.kreg, a.w2_begin, a.w2_end, reg) * p.y);
-    q.z = p.z - lr * (s.z + reg_for(i + 2, a.n_w1, a.ldx, a.kreg, a.w2_begin, a.w2_end, reg) * p.z);
-    q.w = p.w - lr * (s.w + reg_for(i + 3, a.n_w1, a.ldx, a.kreg, a.w2_begin, a.w2_end, reg) * p.w);
-    return q;
+    float r0, r1, r2, r3;
+    if (i < a.n_w1) {
+        const uint32_t u = (uint32_t)i;
+        uint32_t q = __umulhi(u, a.ldx_magic);
+        int col = (int)(u - q * (uint32_t)a.ldx);
+        if (col < 0) col += a.ldx;
+        if (col >= a.ldx) col -= a.ldx;
+        r0 = col < a.kreg ? reg : 0.f;
+        r1 = col + 1 < a.kreg ? reg : 0.f;
+        r2 = col + 2 < a.kreg ? reg : 0.f;
+        r3 = col + 3 < a.kreg ? reg : 0.f;
+    } else {
+        r0 = (i >= a.w2_begin && i < a.w2_end) ? reg : 0.f;
+        r1 = (i + 1 >= a.w2_begin && i + 1 < a.w2_end) ? reg : 0.f;
+        r2 = (i + 2 >= a.w2_begin && i + 2 < a.w2_end) ? reg : 0.f;
+        r3 = (i + 3 >= a.w2_begin && i + 3 < a.w2_end) ? reg : 0.f;
+    }
+    float4 q4;
+    q4.x = p.x - lr * (s.x + r0 * p.x);
+    q4.y = p.y - lr * (s.y + r1 * p.y);
+    q4.z = p.z - lr * (s.z + r2 * p.z);
+    q4.w = p.w - lr * (s.w + r3 * p.w);
+    return q4;
 }
 
 template <bool MC>
@@ -134,25 +168,30 @@ __device__ __forceinline__ void scatter4(const UpdateArgs& a, int64_t i, const f
     }
 }
 
+// Up to kBatch consecutive units are reduced together: every thread first issues the gathers of
+// all its vectors in the batch (one NVLink round trip for the lot), then the SGD, then the stores.
+constexpr int kBatch = 4;
+
 template <bool MC>
-__device__ __forceinline__ void reduce_slice(const UpdateArgs& a, int64_t b, int64_t e, int64_t first,
-                                             int64_t step, float lr, float reg) {
+__device__ __forceinline__ void reduce_batch(const UpdateArgs& a, const int64_t (&b)[kBatch], const int64_t (&e)[kBatch],
+                                             int n, int64_t first, int64_t step, float lr, float reg) {
     const float* mine = a.params_peer[a.rank];
-    int64_t i = b + first;
-    constexpr int U = MC ? 4 : 2;
-    for (; i + (U - 1) * step < e; i += U * step) {
-        float4 s[U], p[U];
+    for (int64_t off = first;; off += step) {
+        float4 s[kBatch], p[kBatch];
+        bool any = false;
 #pragma unroll
-        for (int u = 0; u < U; ++u) s[u] = gather4<MC>(a, i + u * step);
+        for (int j = 0; j < kBatch; ++j)
+            if (j < n && b[j] + off < e[j]) {
+                s[j] = gather4<MC>(a, b[j] + off);
+                any = true;
+            }
+        if (!any) break;
 #pragma unroll
-        for (int u = 0; u < U; ++u) p[u] = *reinterpret_cast<const float4*>(mine + i + u * step);
+        for (int j = 0; j < kBatch; ++j)
+            if (j < n && b[j] + off < e[j]) p[j] = *reinterpret_cast<const float4*>(mine + b[j] + off);
 #pragma unroll
-        for (int u = 0; u < U; ++u) scatter4<MC>(a, i + u * step, sgd4(p[u], s[u], i + u * step, a, lr, reg));
-    }
-    for (; i < e; i += step) {
-        const float4 s = gather4<MC>(a, i);
-        const float4 p = *reinterpret_cast<const float4*>(mine + i);
-        scatter4<MC>(a, i, sgd4(p, s, i, a, lr, reg));
+        for (int j = 0; j < kBatch; ++j)
+            if (j < n && b[j] + off < e[j]) scatter4<MC>(a, b[j] + off, sgd4(p[j], s[j], b[j] + off, a, lr, reg));
     }
 }
 
@@ -175,25 +214,38 @@ __device__ __forceinline__ void run_update(const UpdateArgs& a, int worker, int 
     }
     const int64_t first = ((int64_t)worker * nthreads + tid) * 4, step = (int64_t)nworkers * nthreads * 4;
     // position 0 is the tail (ready first), position u + 1 is unit u
-    for (int pos = 0; pos <= a.nunits; ++pos) {
-        const int flag = pos == 0 ? cme::kPadTail : cme::kPadUnit0 + pos - 1;
-        const int64_t r0 = pos == 0 ? a.n_w1 : (int64_t)(pos - 1) * a.unit_elems;
-        const int64_t r1 = pos == 0 ? a.n_total : min((int64_t)pos * a.unit_elems, a.n_w1);
-        // this rank's slice of the unit
-        const int64_t quads = (r1 - r0) / 4;
-        const int64_t b = r0 + quads * a.rank / a.nranks * 4, e = r0 + quads * (a.rank + 1) / a.nranks * 4;
-        if (b + (int64_t)worker * nthreads * 4 >= e) continue;      // nothing of this unit for my group
+    for (int pos0 = 0; pos0 <= a.nunits && !aborted; pos0 += kBatch) {
+        const int n = min(kBatch, a.nunits + 1 - pos0);
+        int64_t b[kBatch], e[kBatch];
+        bool mine_any = false;
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+            const int pos = pos0 + j;
+            const int64_t r0 = pos == 0 ? a.n_w1 : (int64_t)(pos - 1) * a.unit_elems;
+            const int64_t r1 = pos == 0 ? a.n_total : min((int64_t)pos * a.unit_elems, a.n_w1);
+            // this rank's slice of the unit
+            const int64_t quads = (r1 - r0) / 4;
+            b[j] = r0 + quads * a.rank / a.nranks * 4;
+            e[j] = j < n ? r0 + quads * (a.rank + 1) / a.nranks * 4 : b[j];
+            mine_any = mine_any || (b[j] + (int64_t)worker * nthreads * 4 < e[j]);
+        }
+        if (!mine_any) continue;                                   // nothing of these units for my group
         if (tid == 0) {
-            const bool ok = wait_flag_sys(pad + flag, epoch * (uint32_t)a.nranks, a.timeout_ns);
-            if (!ok) atomicCAS(pad + cme::kPadStatus, 0u, 1u | ((uint32_t)pos << 8));
+            bool ok = true;
+            for (int j = 0; j < n && ok; ++j) {
+                const int pos = pos0 + j;
+                const int flag = pos == 0 ? cme::kPadTail : cme::kPadUnit0 + pos - 1;
+                ok = wait_flag_sys(pad + flag, epoch * (uint32_t)a.nranks, a.timeout_ns);
+                if (!ok) atomicCAS(pad + cme::kPadStatus, 0u, 1u | ((uint32_t)pos << 8));
+            }
             *s_ok = ok;
         }
         asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nthreads) : "memory");
         const bool ok = *reinterpret_cast<volatile uint32_t*>(s_ok) != 0;
         asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nthreads) : "memory");
         if (!ok) { aborted = true; break; }
-        if (a.use_mc) reduce_slice<true>(a, b, e, first, step, lr, reg);
-        else reduce_slice<false>(a, b, e, first, step, lr, reg);
+        if (a.use_mc) reduce_batch<true>(a, b, e, n, first, step, lr, reg);
+        else reduce_batch<false>(a, b, e, n, first, step, lr, reg);
     }
 
     // every group counts itself out; the last one tells every rank "my slices are written",

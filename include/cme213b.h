@@ -97,9 +97,11 @@ int cme_sanitize_compact(const uint8_t* in, size_t n, uint8_t* out, int64_t* out
  * exits, which limits one call to n <= 64 MiB (67108864 bytes); a larger n is
  * rejected with a negative return and a message naming the limit.  The call
  * itself performs no cudaMalloc, cudaFree or other allocating call.
- *   - The first call on each device looks up the array's device address (that
- *     device must be current, as for every call).  Make that first call before
- *     any stream capture is begun on the device.
+ *   - Every call asks the runtime for the array's address on the current device
+ *     (that device must be the one the stream belongs to) and keeps nothing
+ *     between calls, so it stays correct across cudaDeviceReset or a re-created
+ *     context.  The first call on a device also loads the library's code onto
+ *     it: make that first call before any stream capture is begun there.
  *   - All calls on a device share the one array.  It keeps whatever the last call
  *     left in it; this is harmless because a call overwrites every counter it
  *     later reads.  Two calls that can run at the same time on one GPU (different
