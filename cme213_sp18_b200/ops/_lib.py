@@ -65,6 +65,9 @@ _DEV_SIGS = {
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_mlp_dw1_scratch_bytes": [],
+    "cme_mlp_fwd_fused_ok": [c_i64, c_int],
+    "cme_mlp_fwd_scratch_floats": [c_i64],
+    "cme_mlp_fwd_fused": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_i64, c_float, c_i64, c_int, c_int, c_int, c_int, c_int, P],
     "cme_mlp_dw1_sync": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P, P, c_int, c_int, P, P],
     "cme_mlp_update_stream": [P, c_float, c_float, P],
     "cme_mlp_dw1_update": [P, c_i64, c_float, c_float, c_int, P],
@@ -78,7 +81,8 @@ _DEV_SIGS = {
     "cme_peer_barrier": [P, c_int, c_int, c_int, c_u32, c_int, c_int, P],
     "cme_peer_copy": [P, P, c_size_t, P],
 }
-_DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes": c_size_t}
+_DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes": c_size_t,
+                 "cme_mlp_fwd_scratch_floats": c_size_t}
 
 _HOST_SIGS = {
     "cmeh_num_threads": [],

@@ -312,6 +312,25 @@ def mlp_bwd_tail_tc(A1, dz2b, W2T, dZ1, gW2, ldg2: int, rows: int, H: int, ld: i
     _count()
 
 
+def fwd_fused_ok(rows: int, H: int) -> bool:
+    return bool(device_lib().cme_mlp_fwd_fused_ok(rows, H))
+
+
+def fwd_scratch_floats(max_rows: int) -> int:
+    return int(device_lib().cme_mlp_fwd_scratch_floats(max_rows))
+
+
+def mlp_fwd_fused(X, W1c, w2c, b2, labels, A1, dz2, dz2b, loss_sum, pred, gb2, scratch, max_rows: int,
+                  scale: float, rows: int, K: int, H: int, C: int = 10) -> None:
+    """Forward pass in one tensor-core kernel (layer-2 logits ride on the staged A1 tiles) plus the
+    per-row softmax tail; see cme_mlp_fwd_fused."""
+    check(device_lib().cme_mlp_fwd_fused(ptr(X), ptr(W1c), ptr(w2c), ptr(b2), ptr(labels), None, ptr(A1),
+                                         ptr(dz2), ptr(dz2b), ptr(loss_sum), ptr(pred), ptr(gb2), ptr(scratch),
+                                         max_rows, scale, rows, K, H, X.shape[1], A1.shape[1], C, stream_ptr()),
+          "cme_mlp_fwd_fused")
+    _count(2)
+
+
 def mlp_recast_w2(W2, w2c, w2t, H: int, C: int = 10) -> None:
     check(device_lib().cme_mlp_recast_w2(ptr(W2), ptr(w2c), w2c.shape[1], ptr(w2t), H, C, stream_ptr()),
           "cme_mlp_recast_w2")

@@ -154,6 +154,17 @@ int cme_d_sgd(double* p, const double* g, size_t n, double lr, double reg, void*
 int cme_d_axpby(double* c, const double* a, const double* b, double alpha, double beta, size_t n,
                 void* stream);
 
+/* Per-step arguments kept in device memory, so that one recorded CUDA graph serves every
+ * minibatch position and every learning rate: the kernels of a step issued with x_u8 == NULL
+ * read them from plan->step_args; cme_mlp_set_step_args (a one-thread kernel, stream-ordered)
+ * writes them before the step. */
+typedef struct CmeStepArgs {
+    const uint8_t* x_u8;
+    const int32_t* labels;
+    float lr, reg, scale;
+    int reserved;
+} CmeStepArgs;
+
 /* ---- bf16 tensor-core path --------------------------------------------------
  * Row-major activations: X[B][ldx] bf16, A1[B][ldh] bf16, compute weights
  * W1c[Hp][ldx] bf16 (K-major for tcgen05), W2[C][H] fp32.  ldx, ldh are
@@ -220,6 +231,20 @@ int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* 
  * first.  Replaces ref K2 + K10 + K3(dW2) (fpcode/neural_network.cpp:357-378). */
 int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
                         int ldg2, int64_t rows, int H, int ldh, int C, void* stream);
+/* The whole forward pass in one tensor-core kernel plus a per-row tail: A1 = sigmoid(X W1c^T) as
+ * cme_mlp_fwd1, and the layer-2 logits from the same staged tiles (a 256 x 16 x 64 "rider" MMA on
+ * every 128 x 64 chunk of A1 while it sits in shared memory for its TMA store), so A1 is not
+ * read again for layer 2.  The tail adds the partial logits in a fixed order and writes dz2, dz2b,
+ * pred, gb2 (STORED: no zero-fill needed) and loss_sum (+= once) exactly like cme_mlp_fwd2_tc, but
+ * bit-reproducibly.  Needs H rounded up to 64 to be a multiple of 256 and rows >= 256
+ * (cme_mlp_fwd_fused_ok); scratch: cme_mlp_fwd_scratch_floats(max_rows) floats, zeroed once.
+ * Replaces ref fpcode/neural_network.cpp:289-323 (two GEMMs, two bias passes, sigmoid, softmax). */
+int cme_mlp_fwd_fused_ok(int64_t rows, int H);
+size_t cme_mlp_fwd_scratch_floats(int64_t max_rows);
+int cme_mlp_fwd_fused(const void* X, const void* W1c, const void* W2c, const float* b2, const int32_t* labels,
+                      const CmeStepArgs* step_args, void* A1, float* dz2, void* dz2b, float* loss_sum,
+                      int32_t* pred, float* gb2, float* scratch, int64_t max_rows, float scale, int64_t rows,
+                      int K, int H, int ldx, int ldh, int C, void* stream);
 /* W2 (fp32 [C][H]) -> w2c (bf16 [16][ldh]) and, if not NULL, w2t (bf16 [H][64]). */
 int cme_mlp_recast_w2(const float* W2, void* w2c, int ldh, void* w2t, int H, int C, void* stream);
 /* fp32 [rows][ld_src] -> bf16 [rows][ld_dst], first `cols` columns (W2 -> W2c). */
@@ -285,17 +310,6 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
  * [max_rows][ldh], dz2 fp32 [max_rows][16], dz2b bf16 [max_rows][64] (zero-initialised),
  * pred int32 [max_rows], w2c bf16 [16][ldh] and w2t bf16 [Hp][64] (zero-initialised).
  * pads_dev: device array of per-rank flag pads (see cme_peer_barrier), NULL for one rank. */
-/* Per-step arguments kept in device memory, so that one recorded CUDA graph serves every
- * minibatch position and every learning rate: the kernels of a step issued with x_u8 == NULL
- * read them from plan->step_args; cme_mlp_set_step_args (a one-thread kernel, stream-ordered)
- * writes them before the step. */
-typedef struct CmeStepArgs {
-    const uint8_t* x_u8;
-    const int32_t* labels;
-    float lr, reg, scale;
-    int reserved;
-} CmeStepArgs;
-
 typedef struct CmeMlpPlan {
     int D, H, C, Hp, ldx, ldh;
     int rank, nranks;

@@ -317,3 +317,52 @@ def test_tensor_core_tail_fwd2_and_dw2(dev, rows, H):
     assert torch.equal(dZ1f[:, :H], dZ1b[:, :H])
     errf = (gW2f.cpu() - want_gW2).abs().max() / want_gW2.abs().max()
     assert errf < 1e-3, float(errf)
+
+
+@pytest.mark.parametrize("rows,H", [(256, 256), (1000, 1024), (4096, 2048), (8192, 8192), (777, 1000)])
+def test_fwd_fused_rider_matches_two_kernel_forward(dev, rows, H):
+    """A1 and the layer-2 outputs of the one-kernel forward (rider MMAs on the staged A1 tiles +
+    per-row tail) against fp32 PyTorch, and bit-reproducible from call to call."""
+    C, K = 10, 785
+    ldx, ldh = 832, (H + 63) // 64 * 64
+    g = torch.Generator().manual_seed(rows + H)
+    X = torch.zeros((rows, ldx), dtype=torch.bfloat16)
+    X[:, :K - 1] = torch.randint(0, 2, (rows, K - 1), generator=g).to(torch.bfloat16)
+    X[:, K - 1] = 1.0
+    W1 = torch.zeros((ldh, ldx), dtype=torch.bfloat16)
+    W1[:H, :K] = (0.05 * torch.randn((H, K), generator=g)).to(torch.bfloat16)
+    W2 = (0.1 * torch.randn((C, H), generator=g)).float()
+    b2 = torch.randn(C, generator=g).float()
+    labels = torch.randint(0, C, (rows,), generator=g).int()
+    scale = 1.0 / rows
+    w2c = torch.zeros((16, ldh), dtype=torch.bfloat16, device="cuda")
+    dev.f32_to_bf16_2d(W2.cuda(), H, w2c, ldh, C, H)
+    scratch = torch.zeros(dev.fwd_scratch_floats(rows), device="cuda")
+    outs = []
+    for _ in range(2):
+        A1 = torch.full((rows, ldh), 7.0, dtype=torch.bfloat16, device="cuda")
+        dz2 = torch.zeros((rows, 16), device="cuda")
+        dz2b = torch.zeros((rows, 64), dtype=torch.bfloat16, device="cuda")
+        loss = torch.zeros(1, device="cuda")
+        pred = torch.zeros(rows, dtype=torch.int32, device="cuda")
+        gb2 = torch.full((C,), 5.0, device="cuda")
+        dev.mlp_fwd_fused(X.cuda(), W1.cuda(), w2c, b2.cuda(), labels.cuda(), A1, dz2, dz2b, loss, pred, gb2,
+                          scratch, rows, scale, rows, K, H)
+        torch.cuda.synchronize()
+        outs.append((A1, dz2, dz2b, loss, pred, gb2))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    A1, dz2, dz2b, loss, pred, gb2 = outs[0]
+    want_a1 = torch.sigmoid(X[:, :K].float() @ W1[:H, :K].float().T)
+    assert (A1[:, :H].float().cpu() - want_a1).abs().max() < 1e-2
+    a1 = A1[:, :H].float().cpu()
+    z = a1 @ W2.bfloat16().float().T + b2
+    p = torch.softmax(z, dim=1)
+    want_dz2 = (p - torch.nn.functional.one_hot(labels.long(), C)) * scale
+    assert (dz2[:, :C].cpu() - want_dz2).abs().max() < 2e-3 * scale + 1e-7
+    assert float(dz2[:, C:].abs().max()) == 0.0
+    assert torch.equal(dz2b[:, :16].float().cpu(), dz2.cpu().bfloat16().float())
+    want_loss = -torch.log(p[torch.arange(rows), labels.long()]).sum()
+    assert abs(float(loss.item()) - float(want_loss)) < 2e-3 * max(1.0, float(want_loss))
+    assert (pred.cpu().long() == z.argmax(dim=1)).double().mean() > 0.995
+    assert (gb2.cpu() - want_dz2.sum(dim=0)).abs().max() < 1e-4
