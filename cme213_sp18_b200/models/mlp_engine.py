@@ -70,6 +70,9 @@ class MLPEngineBF16:
         self.pads_dev = self.pads.ptr_table_dev()
         self.sync_scratch = torch.zeros(dev.dw1_scratch_words(), dtype=torch.int32, device=d)
         self.step_args = torch.zeros(4, dtype=torch.int64, device=d)             # CmeStepArgs (32 bytes)
+        # partial logits of the one-kernel forward pass (layer 2 rides on the forward GEMM's tiles)
+        fused_fwd = tail == "tc" and self.Hp % 256 == 0 and max_rows >= 256 and not env_flag("CME_NO_FWD_FUSED")
+        self.fwd_scratch = torch.zeros(dev.fwd_scratch_floats(max_rows), device=d) if fused_fwd else None
         self.xb = torch.zeros((max_rows, self.ldx), dtype=torch.bfloat16, device=d)
         self.a1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
         self.dz1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)

@@ -30,15 +30,15 @@ namespace {
 
 using namespace tc;
 
-constexpr int kThreadsF = 320;               // producer warp + MMA warp + 8 epilogue warps
-constexpr int kStagesF = 5;
+constexpr int kThreadsF = 352;               // producer warp + MMA warp + 8 epilogue warps + rider warp
+constexpr int kStagesF = 4;                  // 4 x 32 KB ring + 4 staging chunks + W2c slots fit 227 KB
 constexpr int BKf = 64;
 constexpr int kAB = 128 * BKf * 2;           // 16 KB: this CTA's 128 rows of A, or its half of B
 constexpr int kStg = 128 * 64 * 2;           // 16 KB staging chunk (128 rows x 64 bf16)
 constexpr int kW2Chunk = 8 * 64 * 2;         // 1 KB: this CTA's 8 of the 16 W2c rows, 64 columns
 constexpr int kW2Slot = 4 * kW2Chunk;        // one 256-column tile
 constexpr int kXbuf = 128 * 16 * 4;          // group 1 -> group 0 hand-over of partial logits
-constexpr int kSmemF = kStagesF * 2 * kAB + 2 * kStg + 2 * kW2Slot + kXbuf + 1024 + 512;
+constexpr int kSmemF = kStagesF * 2 * kAB + 4 * kStg + 2 * kW2Slot + kXbuf + 1024 + 512;
 
 struct BarriersF {
     uint64_t full[kStagesF];      // leader: TMA bytes of both CTAs
@@ -47,8 +47,10 @@ struct BarriersF {
     uint64_t tmem_empty[2];       // leader: 8 epilogue warps x 2 CTAs
     uint64_t w_full[2];           // leader: W2c tile bytes of both CTAs
     uint64_t w_empty[2];          // both CTAs (multicast commit after the tile's riders)
-    uint64_t rider_ready[2];      // leader: one arrive per CTA when group g has staged a chunk
-    uint64_t rider_done[2];       // both CTAs (multicast commit): the rider has read the chunk
+    uint64_t rider_ready[4];      // [group * 2 + chunk], leader: one arrive per CTA when the chunk is staged.
+                                  // One barrier per (group, chunk): with one per group a CTA that runs ahead
+                                  // could arrive twice (chunks 0 and 1) and complete a phase on its own
+    uint64_t rider_done[4];       // [group * 2 + chunk], both CTAs (multicast commit): the rider has read the chunk
     uint32_t tmem_base;
 };
 
@@ -79,7 +81,7 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
     uint8_t* sA = smem;
     uint8_t* sB = sA + kStagesF * kAB;
     uint8_t* sC = sB + kStagesF * kAB;
-    uint8_t* sW = sC + 2 * kStg;
+    uint8_t* sW = sC + 4 * kStg;
     float* xbuf = reinterpret_cast<float*>(sW + 2 * kW2Slot);
     BarriersF* bars = (BarriersF*)(reinterpret_cast<uint8_t*>(xbuf) + kXbuf);
 
@@ -101,6 +103,8 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
             mbar_init(&bars->tmem_empty[a], 16);     // 8 epilogue warps x 2 CTAs
             mbar_init(&bars->w_full[a], 1);
             mbar_init(&bars->w_empty[a], 1);
+        }
+        for (int a = 0; a < 4; ++a) {
             mbar_init(&bars->rider_ready[a], 2);     // the group's leader thread of each CTA
             mbar_init(&bars->rider_done[a], 1);
         }
@@ -153,56 +157,17 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0 && cta == 0) {
-            // ---------------- MMA issuer (leader CTA) ----------------
-            // Main products and riders come from this one lane, so the tensor pipe sees them in
-            // issue order.  Every wait below also serves riders that have become ready: the
-            // epilogue cannot release an accumulator stage before its riders have run.
+            // ---------------- MMA issuer (leader CTA): the main products ----------------
             const uint32_t idesc_main = idesc_bf16(256, 256, 0, 0);
-            const uint32_t idesc_rider = idesc_bf16(256, 16, 0, 0);
-            uint32_t rcount[2] = {0, 0};              // riders issued per epilogue group
-            uint32_t tile_riders[2] = {0, 0};         // riders issued for the tile in W2 slot 0 / 1
-            auto serve_riders = [&]() {
-#pragma unroll
-                for (int g = 0; g < 2; ++g) {
-                    const uint32_t r = rcount[g];
-                    if (!mbar_try_wait(&bars->rider_ready[g], r & 1)) continue;
-                    const uint32_t tl = r >> 1, cc = r & 1;
-                    const uint32_t ws = tl & 1, acc = tl & 1;
-                    mbar_wait_bounded(&bars->w_full[ws], (tl >> 1) & 1);
-                    tc_fence_after();
-                    const uint32_t d = tmem_base + acc * 256u + (uint32_t)g * 128u;
-                    const uint32_t a0 = smem_u32(sC + g * kStg);
-                    const uint32_t b0 = smem_u32(sW + ws * kW2Slot + (g * 2 + (int)cc) * kW2Chunk);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        umma_bf16_2cta(d, smem_desc_sw128(a0, 16, 1024) + (uint64_t)(2 * j),
-                                       smem_desc_sw128(b0, 16, 1024) + (uint64_t)(2 * j), idesc_rider,
-                                       (cc | (uint32_t)j) != 0);
-                    umma_commit_2cta(&bars->rider_done[g]);
-                    rcount[g] = r + 1;
-                    if (++tile_riders[ws] == 4) {     // both groups, both chunks: the W2c slot is free
-                        tile_riders[ws] = 0;
-                        umma_commit_2cta(&bars->w_empty[ws]);
-                    }
-                }
-            };
-            auto wait_serving = [&](uint64_t* bar, uint32_t parity) {
-                const long long t0 = clock64();
-                while (!mbar_try_wait(bar, parity)) {
-                    serve_riders();
-                    if (clock64() - t0 > (4ll << 30)) __trap();
-                }
-            };
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            uint32_t tiles_total = 0;
             for (int item = pair; item < items; item += npairs) {
-                for (int t = 0; t < tps; ++t, ++tiles_total) {
-                    wait_serving(&bars->tmem_empty[acc], acc_phase ^ 1);
+                for (int t = 0; t < tps; ++t) {
+                    mbar_wait_bounded(&bars->tmem_empty[acc], acc_phase ^ 1);
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
                     for (int kb = 0; kb < nk; ++kb) {
-                        wait_serving(&bars->full[stage], phase);
+                        mbar_wait_bounded(&bars->full[stage], phase);
                         tc_fence_after();
                         const int kvalid = min(BKf, K - kb * BKf);
                         const int nmma = (kvalid + 15) >> 4;
@@ -213,19 +178,51 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
                                            (kb | j) != 0);
                         umma_commit_2cta(&bars->empty[stage]);
                         if (++stage == kStagesF) { stage = 0; phase ^= 1; }
-                        serve_riders();
                     }
                     umma_commit_2cta(&bars->tmem_full[acc]);
                     acc ^= 1;
                     if (acc == 0) acc_phase ^= 1;
                 }
             }
-            // the riders of the last tiles
-            {
-                const long long t0 = clock64();
-                while (rcount[0] < 2 * tiles_total || rcount[1] < 2 * tiles_total) {
-                    serve_riders();
-                    if (clock64() - t0 > (4ll << 30)) __trap();
+        }
+        __syncwarp();
+    } else if (warp == 10) {
+        if (lane == 0 && cta == 0) {
+            // ---------------- rider issuer (leader CTA) ----------------
+            // A lane of its own, so the main issuer never polls: it sleeps on the "chunk staged"
+            // barriers and issues the 256 x 16 x 64 product of each staged chunk with the W2c tile.
+            // Riders of one group run in chunk order (chunk 1 accumulates on chunk 0); against the
+            // main products no order is needed, they write other TMEM columns.
+            const uint32_t idesc_rider = idesc_bf16(256, 16, 0, 0);
+            uint32_t tl = 0;
+            for (int item = pair; item < items; item += npairs) {
+                for (int t = 0; t < tps; ++t, ++tl) {
+                    const uint32_t ws = tl & 1, acc = tl & 1;
+                    mbar_wait_bounded(&bars->w_full[ws], (tl >> 1) & 1);
+                    uint32_t pending = 0xF;                       // bit g * 2 + cc
+                    const long long t0 = clock64();
+                    while (pending) {
+                        if (clock64() - t0 > (4ll << 30)) __trap();
+#pragma unroll
+                        for (int g = 0; g < 2; ++g) {
+                            const int cc = (pending >> (g * 2)) & 1 ? 0 : 1;       // chunk 0 before chunk 1
+                            const int idx = g * 2 + cc;
+                            if (!((pending >> idx) & 1)) continue;
+                            if (!mbar_try_wait(&bars->rider_ready[idx], tl & 1)) continue;
+                            tc_fence_after();
+                            const uint32_t d = tmem_base + acc * 256u + (uint32_t)g * 128u;
+                            const uint32_t a0 = smem_u32(sC + idx * kStg);
+                            const uint32_t b0 = smem_u32(sW + ws * kW2Slot + idx * kW2Chunk);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                umma_bf16_2cta(d, smem_desc_sw128(a0, 16, 1024) + (uint64_t)(2 * j),
+                                               smem_desc_sw128(b0, 16, 1024) + (uint64_t)(2 * j), idesc_rider,
+                                               (cc | j) != 0);
+                            umma_commit_2cta(&bars->rider_done[idx]);
+                            pending &= ~(1u << idx);
+                        }
+                    }
+                    umma_commit_2cta(&bars->w_empty[ws]);         // the W2c slot is free again
                 }
             }
         }
@@ -238,7 +235,6 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
         const int grp = (warp - 2) >> 2;
         const int row = q * 32 + lane;
         const bool leader = (((warp - 2) & 3) == 0 && lane == 0);
-        uint8_t* stg = sC + grp * kStg;
         int acc = 0;
         uint32_t acc_phase = 0;
         uint32_t rid = 0;                                  // chunks this group has staged
@@ -266,10 +262,16 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
                         pk[e] = sigmoid2_bf16(__uint_as_float(v0[2 * e]), __uint_as_float(v0[2 * e + 1]));
                         pk[16 + e] = sigmoid2_bf16(__uint_as_float(v1[2 * e]), __uint_as_float(v1[2 * e + 1]));
                     }
-                    // the staging buffer is free once the previous chunk's TMA store has read it
-                    // AND the rider that multiplied it has completed
-                    if (leader) tma_store_wait_read<0>();
-                    if (rid > 0) mbar_wait_bounded(&bars->rider_done[grp], (rid - 1) & 1);
+                    // Two staging buffers per group (one per chunk of the tile), so staging chunk 1
+                    // does not wait for the rider of chunk 0, which sits in the tensor pipe behind
+                    // every main MMA already issued.  Buffer cc is free once the TMA store of the
+                    // previous tile's chunk cc has read it (at most one younger store pending) AND
+                    // that chunk's rider has completed (one barrier per (group, chunk): it completes
+                    // once per tile, so its parity names the tile).
+                    uint8_t* stg = sC + (grp * 2 + cc) * kStg;
+                    const uint32_t tl = rid >> 1;                      // tiles this pair has finished
+                    if (leader) tma_store_wait_read<1>();
+                    if (tl > 0) mbar_wait_bounded(&bars->rider_done[grp * 2 + cc], (tl - 1) & 1);
                     named_bar_sync(1 + grp, 128);
 #pragma unroll
                     for (int chunk = 0; chunk < 8; ++chunk) {
@@ -283,12 +285,12 @@ fwd_rider_kernel(const __grid_constant__ CUtensorMap tmA /* X   [rows][K]  box 6
                     if (leader) {
                         tma_store_2d(&tmC, stg, n0 + c * 64, m0);
                         tma_store_commit();
-                        mbar_arrive_leader_release(&bars->rider_ready[grp]);
+                        mbar_arrive_leader_release(&bars->rider_ready[grp * 2 + cc]);
                     }
                     ++rid;
                 }
                 // both riders of this group for this tile: 16 partial logits per row
-                mbar_wait_bounded(&bars->rider_done[grp], (rid - 1) & 1);
+                mbar_wait_bounded(&bars->rider_done[grp * 2 + 1], ((rid >> 1) - 1) & 1);
                 tc_fence_after();
                 uint32_t z[16];
                 tmem_ld_32x16(t_row + (uint32_t)(grp * 128), z);

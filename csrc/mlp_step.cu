@@ -9,7 +9,8 @@
 //
 // Schedule:
 //   side   memset of the W2 / b2 gradient tail (a few hundred KB), hidden under staging + forward
-//   main   staging, forward GEMM + sigmoid, layer 2 + softmax + CE, backward tail (dZ1 + dW2)
+//   main   staging, forward GEMM + sigmoid with the layer-2 logits riding on its staged tiles,
+//          per-row softmax + CE tail, backward tail (dZ1 + dW2)
 //   main   dW1 GEMM + update in ONE kernel: the GEMM publishes every unit (256 rows of W1) of the
 //          gradient as it completes, and four extra warps in each of its CTAs reduce the unit
 //          over NVLink as soon as every rank has published it, apply SGD and replicate the weights
@@ -96,10 +97,18 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
     CME_CUDA(cudaMemsetAsync(grads + g.o_w2, 0, sizeof(float) * (size_t)(g.n_total - g.o_w2), side_s));
     if (side_stream) CME_CUDA(cudaEventRecord(ev(1), side_s));
     if ((rc = cme_u8_to_bf16_rows_ind(x_u8, sa, p->xb, rows, g.D, g.ldx, 1, stream))) return rc;
-    if ((rc = cme_mlp_fwd1(p->xb, p->w1c[p->rank], nullptr, p->a1, rows, g.K, g.H, g.ldx, g.ldh, stream))) return rc;
-    if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
-    if ((rc = cme_mlp_fwd2_tc_ind(p->a1, p->w2c, params + g.o_b2, labels, sa, p->dz2, p->dz2b, loss_sum, p->pred,
-                                  grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
+    if (p->fwd_scratch && cme_mlp_fwd_fused_ok(rows, g.H)) {
+        // forward pass in one kernel: the layer-2 logits ride on the A1 tiles while they are staged
+        if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
+        if ((rc = cme_mlp_fwd_fused(p->xb, p->w1c[p->rank], p->w2c, params + g.o_b2, labels, sa, p->a1, p->dz2,
+                                    p->dz2b, loss_sum, p->pred, grads + g.o_b2, p->fwd_scratch, p->max_rows, scale,
+                                    rows, g.K, g.H, g.ldx, g.ldh, g.C, stream))) return rc;
+    } else {
+        if ((rc = cme_mlp_fwd1(p->xb, p->w1c[p->rank], nullptr, p->a1, rows, g.K, g.H, g.ldx, g.ldh, stream))) return rc;
+        if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
+        if ((rc = cme_mlp_fwd2_tc_ind(p->a1, p->w2c, params + g.o_b2, labels, sa, p->dz2, p->dz2b, loss_sum, p->pred,
+                                      grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
+    }
     if ((rc = cme_mlp_bwd_tail_tc(p->a1, p->dz2b, p->w2t, p->dz1, grads + g.o_w2, g.H, rows, g.H, g.ldh, g.C,
                                   stream))) return rc;
     if (p->overlap) {
@@ -138,6 +147,12 @@ int cme_mlp_plan_init_sync(CmeMlpPlan* p) {
     p->pads_dev = table;
     p->sync_scratch = scratch;
     p->step_args = sa;
+    p->fwd_scratch = nullptr;
+    if (p->Hp % 256 == 0 && p->max_rows >= 256) {
+        const size_t n = cme_mlp_fwd_scratch_floats(p->max_rows);
+        CME_CUDA(cudaMalloc(&p->fwd_scratch, n * sizeof(float)));
+        CME_CUDA(cudaMemset(p->fwd_scratch, 0, n * sizeof(float)));
+    }
     p->unit_rows = p->Hp >= 512 ? 256 : 128;
     p->overlap = 1;
     return 0;
@@ -149,12 +164,14 @@ int cme_mlp_plan_free_sync(CmeMlpPlan* p) {
     if (p->pads_dev) cudaFree((void*)p->pads_dev);
     if (p->sync_scratch) cudaFree(p->sync_scratch);
     if (p->step_args) cudaFree(p->step_args);
+    if (p->fwd_scratch) cudaFree(p->fwd_scratch);
+    p->fwd_scratch = nullptr;
     p->pad_local = nullptr, p->pads_dev = nullptr, p->sync_scratch = nullptr, p->step_args = nullptr;
     return 0;
 }
 
 int cme_mlp_step_launches(const CmeMlpPlan* p) {
-    // staging, forward GEMM, layer 2, backward tail, dW1 (+ update), re-cast
+    // staging, forward GEMM, layer 2 (or its per-row tail), backward tail, dW1 (+ update), re-cast
     return p ? (p->overlap ? 6 : 7) : 0;
 }
 

@@ -341,6 +341,9 @@ typedef struct CmeMlpPlan {
     void* sync_scratch;
     /* Optional: device memory for the indirect step arguments (see CmeStepArgs). */
     CmeStepArgs* step_args;
+    /* Optional: cme_mlp_fwd_scratch_floats(max_rows) floats, zeroed once.  When present (and the
+     * shape allows it, cme_mlp_fwd_fused_ok) the step runs the forward pass as cme_mlp_fwd_fused. */
+    float* fwd_scratch;
 } CmeMlpPlan;
 /* One whole training step on `rows` local samples (uint8 pixels x_u8 [rows][D], labels
  * int32 [rows], both device pointers; x_u8 may be peer-mapped): staging, forward, backward,
