@@ -73,6 +73,9 @@ class MLPEngineBF16:
         # partial logits of the one-kernel forward pass (layer 2 rides on the forward GEMM's tiles)
         fused_fwd = tail == "tc" and self.Hp % 256 == 0 and max_rows >= 256 and not env_flag("CME_NO_FWD_FUSED")
         self.fwd_scratch = torch.zeros(dev.fwd_scratch_floats(max_rows), device=d) if fused_fwd else None
+        # per-CTA slots of the dW2 product, added up in CTA order (bit-reproducible gradients)
+        n_dw2 = int(dev.device_lib().cme_mlp_bwd_tail_scratch_floats(self.Hh)) if torch.cuda.is_available() else 0
+        self.dw2_scratch = torch.zeros(n_dw2, device=d) if (tail == "tc" and n_dw2) else None
         self.xb = torch.zeros((max_rows, self.ldx), dtype=torch.bfloat16, device=d)
         self.a1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)
         self.dz1 = torch.zeros((max_rows, self.ldh), dtype=torch.bfloat16, device=d)

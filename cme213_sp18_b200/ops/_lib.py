@@ -65,6 +65,8 @@ _DEV_SIGS = {
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_mlp_dw1_scratch_bytes": [],
+    "cme_mlp_bwd_tail_scratch_floats": [c_int],
+    "cme_mlp_bwd_tail_det": [P, P, P, P, P, c_int, c_i64, c_int, c_int, c_int, P, P],
     "cme_mlp_fwd_fused_ok": [c_i64, c_int],
     "cme_mlp_fwd_scratch_floats": [c_i64],
     "cme_mlp_fwd_fused": [P, P, P, P, P, P, P, P, P, P, P, P, P, c_i64, c_float, c_i64, c_int, c_int, c_int, c_int, c_int, P],
@@ -82,7 +84,7 @@ _DEV_SIGS = {
     "cme_peer_copy": [P, P, c_size_t, P],
 }
 _DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes": c_size_t,
-                 "cme_mlp_fwd_scratch_floats": c_size_t}
+                 "cme_mlp_fwd_scratch_floats": c_size_t, "cme_mlp_bwd_tail_scratch_floats": c_size_t}
 
 _HOST_SIGS = {
     "cmeh_num_threads": [],

@@ -418,7 +418,8 @@ def _plan_type():
                     ("pads_dev", C.c_void_p), ("overlap", C.c_int), ("use_mc", C.c_int),
                     ("grads_mc", C.c_void_p), ("params_mc", C.c_void_p), ("w1c_mc", C.c_void_p),
                     ("unit_rows", C.c_int), ("timeout_ms", C.c_int), ("pad_local", C.c_void_p),
-                    ("sync_scratch", C.c_void_p), ("step_args", C.c_void_p), ("fwd_scratch", C.c_void_p)]
+                    ("sync_scratch", C.c_void_p), ("step_args", C.c_void_p), ("fwd_scratch", C.c_void_p),
+                    ("dw2_scratch", C.c_void_p)]
 
     return CmeMlpPlan
 
@@ -439,6 +440,7 @@ def make_mlp_plan(eng):
     p.sync_scratch = ptr(eng.sync_scratch)
     p.step_args = ptr(eng.step_args)
     p.fwd_scratch = ptr(eng.fwd_scratch)
+    p.dw2_scratch = ptr(eng.dw2_scratch)
     p.unit_rows, p.timeout_ms = eng.unit_rows, eng.timeout_ms
     p.overlap, p.use_mc = int(eng.overlap), int(eng.use_mc)
     if eng.use_mc:

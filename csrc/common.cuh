@@ -105,6 +105,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// flag bump without a fence of its own: the caller issues ONE fence.sys and then bumps the flag on
+// every rank (a .release on each of 8 bumps would be 8 fences in a row, microseconds each)
+__device__ __forceinline__ void red_relaxed_sys_add(uint32_t* p, uint32_t v) {
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

@@ -626,8 +626,8 @@ __device__ __forceinline__ void dw_publish(const DwSync& sy, uint32_t* ctr, int 
     if ((int)old + 1 == parts) {
         sy.unit_ctr[unit] = 0;
         if (sy.pads) {
-            __threadfence_system();
-            for (int r = 0; r < sy.nranks; ++r) cme::red_release_sys_add(sy.pads[r] + cme::kPadUnit0 + unit, 1u);
+            __threadfence_system();                 // one fence, then the bumps (see red_relaxed_sys_add)
+            for (int r = 0; r < sy.nranks; ++r) cme::red_relaxed_sys_add(sy.pads[r] + cme::kPadUnit0 + unit, 1u);
         }
     }
 }
@@ -1184,7 +1184,8 @@ bwd_tail_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b [rows][16 of 64]
                 const __grid_constant__ CUtensorMap tmW /* W2T  [H][16 of 64]    */,
                 const __grid_constant__ CUtensorMap tmA1 /* A1  [rows][H] load   */,
                 const __grid_constant__ CUtensorMap tmZ /* dZ1  [rows][H] store  */,
-                float* __restrict__ gW2, int ldg2, int H, int C, int m_tiles, int n_tiles) {
+                float* __restrict__ gW2, int ldg2, int H, int C, int m_tiles, int n_tiles,
+                float* __restrict__ part /* null: add into gW2; else slot (CTA + column block) x 16 x 128 */) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* sD = smem;                               // 2 x 16 KB: dz2b tiles
@@ -1378,7 +1379,13 @@ bwd_tail_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b [rows][16 of 64]
                 tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + kD2Col, v);
                 tmem_ld_wait();
                 const int h = n0 + row;
-                if (h < H) {
+                if (part) {
+                    // deterministic mode: this CTA's share of the column block goes to a slot of its
+                    // own (CTA index + column block is unique, see dw2_reduce_kernel), stored
+                    float* dst = part + ((size_t)blockIdx.x + (size_t)n) * 2048 + row;
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) dst[c * 128] = __uint_as_float(v[c]);
+                } else if (h < H) {
 #pragma unroll
                     for (int c = 0; c < 16; ++c)
                         if (c < C) atomicAdd(gW2 + (size_t)c * ldg2 + h, __uint_as_float(v[c]));
@@ -1398,6 +1405,33 @@ bwd_tail_kernel(const __grid_constant__ CUtensorMap tmD /* dz2b [rows][16 of 64]
     }
 }
 
+// gW2[c][h] = sum over the CTAs of bwd_tail_kernel that worked on h's column block, in CTA order.
+// CTA b covered tiles [T*b/G, T*(b+1)/G) of the column-major tile order (T = m_tiles * n_tiles),
+// so the CTAs of column block n are consecutive and (b, n) -> slot b + n is one-to-one.
+__global__ void __launch_bounds__(128)
+dw2_reduce_kernel(const float* __restrict__ part, float* __restrict__ gW2, int ldg2, int H, int C,
+                  int m_tiles, int n_tiles, int G) {
+    const int n = blockIdx.x, c = blockIdx.y, r = threadIdx.x;
+    const int h = n * 128 + r;
+    const long long T = (long long)m_tiles * n_tiles, lo = (long long)n * m_tiles, hi = lo + m_tiles;
+    int b0 = (int)(lo * G / T);
+    while (b0 < G && T * (b0 + 1) / G <= lo) ++b0;
+    int b1 = b0;
+    while (b1 < G && T * b1 / G < hi) ++b1;                      // every CTA has tiles (G <= T)
+    const float* src = part + (size_t)n * 2048 + (size_t)c * 128 + r;
+    float acc = 0.f;
+    int b = b0;
+    for (; b + 8 <= b1; b += 8) {                                // loads first, then the adds in CTA order
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = src[(size_t)(b + k) * 2048];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc += v[k];
+    }
+    for (; b < b1; ++b) acc += src[(size_t)b * 2048];
+    if (h < H && c < C) gW2[(size_t)c * ldg2 + h] = acc;
+}
+
 // =============================================================================
 // host side: tensor maps and launches
 // =============================================================================
@@ -1407,6 +1441,19 @@ using tc_host::opt_in_smem;
 // Number of k-chunks for the (k-chunk, m, n) schedule: the smallest split (at most 16, at least
 // 8 k-blocks per chunk) whose item count fills `sms` CTAs with the least idle tail.
 int choose_ksplit(int tiles_mn, int kb_total, int sms) {
+    // Small problems (every item of every chunk runs at once): the chunks of a tile then finish
+    // together and their epilogues go one after the other (ordered split-K), so the time is about
+    // kb/s k-blocks (~0.27 us each) plus s epilogues (~2.5 us each): pick the s that minimises it.
+    if ((long long)tiles_mn * 16 <= sms || (long long)tiles_mn * std::max(1, kb_total / 8) <= sms) {
+        int bs = 1;
+        double bt = 1e30;
+        for (int s = 1; s <= 16 && (long long)tiles_mn * s <= sms; ++s) {
+            if (s > 1 && kb_total / s < 8) break;
+            const double t = 0.27 * ((kb_total + s - 1) / s) + 2.5 * s;
+            if (t < bt) { bt = t; bs = s; }
+        }
+        return bs;
+    }
     int best = 1;
     double best_eff = 0.0;
     for (int s = 1; s <= 16; ++s) {
@@ -1709,6 +1756,16 @@ int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* 
 
 int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
                         int ldg2, int64_t rows, int H, int ldh, int C, void* stream) {
+    return cme_mlp_bwd_tail_det(A1, dz2b, W2T, dZ1, gW2, ldg2, rows, H, ldh, C, nullptr, stream);
+}
+
+size_t cme_mlp_bwd_tail_scratch_floats(int H) {
+    // one 16 x 128 slot per (CTA, column block) pair: at most SMs + column blocks of them
+    return ((size_t)cme::sm_count() + (size_t)(H + 127) / 128 + 1) * 2048;
+}
+
+int cme_mlp_bwd_tail_det(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
+                         int ldg2, int64_t rows, int H, int ldh, int C, float* part, void* stream) {
     CME_CHECK_ARG(A1 && dz2b && W2T && dZ1 && gW2 && rows > 0 && H > 0, "cme_mlp_bwd_tail_tc: bad argument");
     CME_CHECK_ARG(ldh % 8 == 0 && ldh >= H && C >= 1 && C <= 16, "cme_mlp_bwd_tail_tc: ldh (%d), C (%d)", ldh, C);
     CME_CHECK_ARG(rows < (1ll << 31), "cme_mlp_bwd_tail_tc: too many rows");
@@ -1724,8 +1781,13 @@ int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void*
     const int grid = (int)std::min<long long>(tiles, cme::sm_count());
     CME_CHECK_ARG(ldg2 >= H, "cme_mlp_bwd_tail_tc: ldg2 (%d) < H (%d)", ldg2, H);
     bwd_tail_kernel<<<grid, kThreads, kSmemFt, cme::as_stream(stream)>>>(tmD, tmW, tmA1, tmZ, gW2, ldg2,
-                                                                        H, C, m_tiles, n_tiles);
+                                                                        H, C, m_tiles, n_tiles, part);
     CME_LAUNCH_CHECK();
+    if (part) {
+        dw2_reduce_kernel<<<dim3(n_tiles, 16), 128, 0, cme::as_stream(stream)>>>(part, gW2, ldg2, H, C, m_tiles,
+                                                                                 n_tiles, grid);
+        CME_LAUNCH_CHECK();
+    }
     return 0;
 }
 

@@ -8,14 +8,16 @@
 // synchronisation.  The Python engine issues its steps through this function too.
 //
 // Schedule:
-//   side   memset of the W2 / b2 gradient tail (a few hundred KB), hidden under staging + forward
 //   main   staging, forward GEMM + sigmoid with the layer-2 logits riding on its staged tiles,
 //          per-row softmax + CE tail, backward tail (dZ1 + dW2)
 //   main   dW1 GEMM + update in ONE kernel: the GEMM publishes every unit (256 rows of W1) of the
 //          gradient as it completes, and four extra warps in each of its CTAs reduce the unit
 //          over NVLink as soon as every rank has published it, apply SGD and replicate the weights
 //   main   re-cast W2
-// Nothing zero-fills the W1 gradient (the first k-chunk of every tile stores), and there are no
+// Nothing zero-fills a gradient (the first k-chunk of every dW1 tile stores; dW2 is added up from
+// per-CTA slots in CTA order; db2 and the loss from per-block partials), so the step is
+// bit-reproducible; shapes the one-kernel forward does not take fall back to atomics on a zeroed
+// tail.  There are no
 // barrier launches: the flags live inside the kernel.  With plan->overlap == 0 the update runs
 // as a kernel of its own behind the GEMM; the arithmetic and the owner of every slice of the
 // sharded fp32 master are the same either way.
@@ -89,17 +91,23 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
     auto ev = [&](int i) { return reinterpret_cast<cudaEvent_t>(events[i]); };
     int rc;
 
-    if (side_stream) {
-        CME_CUDA(cudaEventRecord(ev(0), main_s));
-        CME_CUDA(cudaStreamWaitEvent(side_s, ev(0), 0));
+    const bool fused_fwd = p->fwd_scratch && cme_mlp_fwd_fused_ok(rows, g.H);
+    // With the one-kernel forward (db2 stored by its tail) and the slot-wise dW2 every gradient is
+    // STORED in a fixed order: nothing to zero, nothing on the side stream.  Otherwise dW2 / db2
+    // are accumulated with atomics and the tail of the gradient vector is zeroed first.
+    const bool need_zero = !(fused_fwd && p->dw2_scratch);
+    if (need_zero) {
+        if (side_stream) {
+            CME_CUDA(cudaEventRecord(ev(0), main_s));
+            CME_CUDA(cudaStreamWaitEvent(side_s, ev(0), 0));
+        }
+        CME_CUDA(cudaMemsetAsync(grads + g.o_w2, 0, sizeof(float) * (size_t)(g.n_total - g.o_w2), side_s));
+        if (side_stream) CME_CUDA(cudaEventRecord(ev(1), side_s));
     }
-    // dW2 and db2 are still accumulated with atomics: zero the tail (W1's gradient is stored)
-    CME_CUDA(cudaMemsetAsync(grads + g.o_w2, 0, sizeof(float) * (size_t)(g.n_total - g.o_w2), side_s));
-    if (side_stream) CME_CUDA(cudaEventRecord(ev(1), side_s));
     if ((rc = cme_u8_to_bf16_rows_ind(x_u8, sa, p->xb, rows, g.D, g.ldx, 1, stream))) return rc;
-    if (p->fwd_scratch && cme_mlp_fwd_fused_ok(rows, g.H)) {
+    if (fused_fwd) {
         // forward pass in one kernel: the layer-2 logits ride on the A1 tiles while they are staged
-        if (side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
+        if (need_zero && side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
         if ((rc = cme_mlp_fwd_fused(p->xb, p->w1c[p->rank], p->w2c, params + g.o_b2, labels, sa, p->a1, p->dz2,
                                     p->dz2b, loss_sum, p->pred, grads + g.o_b2, p->fwd_scratch, p->max_rows, scale,
                                     rows, g.K, g.H, g.ldx, g.ldh, g.C, stream))) return rc;
@@ -109,8 +117,8 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
         if ((rc = cme_mlp_fwd2_tc_ind(p->a1, p->w2c, params + g.o_b2, labels, sa, p->dz2, p->dz2b, loss_sum, p->pred,
                                       grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
     }
-    if ((rc = cme_mlp_bwd_tail_tc(p->a1, p->dz2b, p->w2t, p->dz1, grads + g.o_w2, g.H, rows, g.H, g.ldh, g.C,
-                                  stream))) return rc;
+    if ((rc = cme_mlp_bwd_tail_det(p->a1, p->dz2b, p->w2t, p->dz1, grads + g.o_w2, g.H, rows, g.H, g.ldh, g.C,
+                                   p->dw2_scratch, stream))) return rc;
     if (p->overlap) {
         // ONE kernel: the dW1 GEMM with the update warps inside it
         if ((rc = cme_mlp_dw1_update(p, rows, lr, reg, sa != nullptr, stream))) return rc;
@@ -153,6 +161,11 @@ int cme_mlp_plan_init_sync(CmeMlpPlan* p) {
         CME_CUDA(cudaMalloc(&p->fwd_scratch, n * sizeof(float)));
         CME_CUDA(cudaMemset(p->fwd_scratch, 0, n * sizeof(float)));
     }
+    {
+        const size_t n = cme_mlp_bwd_tail_scratch_floats(p->H);
+        CME_CUDA(cudaMalloc(&p->dw2_scratch, n * sizeof(float)));
+        CME_CUDA(cudaMemset(p->dw2_scratch, 0, n * sizeof(float)));
+    }
     p->unit_rows = p->Hp >= 512 ? 256 : 128;
     p->overlap = 1;
     return 0;
@@ -165,14 +178,15 @@ int cme_mlp_plan_free_sync(CmeMlpPlan* p) {
     if (p->sync_scratch) cudaFree(p->sync_scratch);
     if (p->step_args) cudaFree(p->step_args);
     if (p->fwd_scratch) cudaFree(p->fwd_scratch);
-    p->fwd_scratch = nullptr;
+    if (p->dw2_scratch) cudaFree(p->dw2_scratch);
+    p->fwd_scratch = nullptr, p->dw2_scratch = nullptr;
     p->pad_local = nullptr, p->pads_dev = nullptr, p->sync_scratch = nullptr, p->step_args = nullptr;
     return 0;
 }
 
 int cme_mlp_step_launches(const CmeMlpPlan* p) {
     // staging, forward GEMM, layer 2 (or its per-row tail), backward tail, dW1 (+ update), re-cast
-    return p ? (p->overlap ? 6 : 7) : 0;
+    return p ? (p->overlap ? 6 : 7) + (p->dw2_scratch ? 1 : 0) : 0;
 }
 
 }  // extern "C"

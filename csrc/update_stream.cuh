@@ -210,7 +210,7 @@ __device__ __forceinline__ void run_update(const UpdateArgs& a, int worker, int 
     // stream order put this kernel after the backward tail: my W2 / b2 gradients are complete
     if (worker == 0 && tid < a.nranks) {
         __threadfence_system();
-        cme::red_release_sys_add(a.pads[tid] + cme::kPadTail, 1u);
+        cme::red_relaxed_sys_add(a.pads[tid] + cme::kPadTail, 1u);
     }
     const int64_t first = ((int64_t)worker * nthreads + tid) * 4, step = (int64_t)nworkers * nthreads * 4;
     // position 0 is the tail (ready first), position u + 1 is unit u
@@ -260,8 +260,10 @@ __device__ __forceinline__ void run_update(const UpdateArgs& a, int worker, int 
         last = __shfl_sync(0xffffffffu, last, 0);
         if (last) {
             if (tid == 0) pad[cme::kPadDoneCtr] = 0;
+            // every group fenced its stores at system scope before it counted itself out, and this
+            // thread has seen all the counts: one more fence orders those observations before the bumps
             __threadfence_system();
-            if (tid < a.nranks) cme::red_release_sys_add(a.pads[tid] + cme::kPadDone0 + a.rank, 1u);
+            if (tid < a.nranks) cme::red_relaxed_sys_add(a.pads[tid] + cme::kPadDone0 + a.rank, 1u);
             bool ok = true;
             const bool skip = aborted || *reinterpret_cast<volatile uint32_t*>(pad + cme::kPadStatus) != 0;
             if (tid < a.nranks && !skip) ok = wait_flag_sys(pad + cme::kPadDone0 + tid, epoch, a.timeout_ns);

@@ -231,6 +231,12 @@ int cme_mlp_bwd_dz1_tc(const void* A1, const void* dz2b, const void* W2T, void* 
  * first.  Replaces ref K2 + K10 + K3(dW2) (fpcode/neural_network.cpp:357-378). */
 int cme_mlp_bwd_tail_tc(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
                         int ldg2, int64_t rows, int H, int ldh, int C, void* stream);
+/* The same pass with a bit-reproducible dW2: every CTA stores its share of a column block into
+ * a slot of `part` (cme_mlp_bwd_tail_scratch_floats(H) floats) and a small second kernel adds
+ * the slots in CTA order and STORES gW2 (no zero-fill needed).  part == NULL: as above. */
+size_t cme_mlp_bwd_tail_scratch_floats(int H);
+int cme_mlp_bwd_tail_det(const void* A1, const void* dz2b, const void* W2T, void* dZ1, float* gW2,
+                         int ldg2, int64_t rows, int H, int ldh, int C, float* part, void* stream);
 /* The whole forward pass in one tensor-core kernel plus a per-row tail: A1 = sigmoid(X W1c^T) as
  * cme_mlp_fwd1, and the layer-2 logits from the same staged tiles (a 256 x 16 x 64 "rider" MMA on
  * every 128 x 64 chunk of A1 while it sits in shared memory for its TMA store), so A1 is not
@@ -344,6 +350,10 @@ typedef struct CmeMlpPlan {
     /* Optional: cme_mlp_fwd_scratch_floats(max_rows) floats, zeroed once.  When present (and the
      * shape allows it, cme_mlp_fwd_fused_ok) the step runs the forward pass as cme_mlp_fwd_fused. */
     float* fwd_scratch;
+    /* Optional: cme_mlp_bwd_tail_scratch_floats(H) floats.  When present dW2 is summed in a fixed
+     * order (cme_mlp_bwd_tail_det); with fwd_scratch too the whole step is bit-reproducible and
+     * nothing in it needs a zero-fill. */
+    float* dw2_scratch;
 } CmeMlpPlan;
 /* One whole training step on `rows` local samples (uint8 pixels x_u8 [rows][D], labels
  * int32 [rows], both device pointers; x_u8 may be peer-mapped): staging, forward, backward,

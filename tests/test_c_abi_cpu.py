@@ -92,8 +92,8 @@ def test_plan_struct_layout_matches_the_header():
             names.append(re.sub(r"\[.*\]", "", part.strip().split()[-1].lstrip("*")))
     mirror = [f for f, _ in dev._plan_type()._fields_]
     assert names == mirror, (names, mirror)
-    # 8 ints, int64, 3 x 16 pointers, 8 pointers, pads_dev, 2 ints, 3 pointers, 2 ints, 4 pointers
-    assert C.sizeof(dev._plan_type()) == 8 * 4 + 8 + 3 * 16 * 8 + 8 * 8 + 8 + 2 * 4 + 3 * 8 + 2 * 4 + 4 * 8
+    # 8 ints, int64, 3 x 16 pointers, 8 pointers, pads_dev, 2 ints, 3 pointers, 2 ints, 5 pointers
+    assert C.sizeof(dev._plan_type()) == 8 * 4 + 8 + 3 * 16 * 8 + 8 * 8 + 8 + 2 * 4 + 3 * 8 + 2 * 4 + 5 * 8
 
 
 def test_master_shard_bounds_agree_between_python_and_c():
