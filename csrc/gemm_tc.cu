@@ -1557,14 +1557,22 @@ static int dw1_check_args(const void* dZ1, const void* X, float* gW1, int64_t ro
 
 static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
                       int ldh, int ldg, uint32_t* scratch, uint32_t* const* pads, int nranks,
-                      int unit_rows, uint32_t* status, const upd::UpdateArgs* fused, cudaStream_t st) {
+                      int unit_rows, uint32_t* status, const upd::UpdateArgs* fused, cudaStream_t st,
+                      bool* fused_used = nullptr) {
     CME_CHECK_ARG(unit_rows == 128 || unit_rows == 256, "cme_mlp_dw1: unit_rows is 128 or 256 (got %d)", unit_rows);
     int rc0 = dw1_check_args(dZ1, X, gW1, rows, K, H, ldx, ldh, ldg);
     if (rc0) return rc0;
     CME_CHECK_ARG(scratch, "cme_mlp_dw1: no scratch");
     upd::UpdateArgs ua{};
     if (fused) ua = *fused;
-    const int threads = ua.enabled ? kThreadsDw : kThreads;
+    // The update warps are 128 threads per CTA of THIS grid.  A small GEMM (few CTAs) would leave
+    // each of them dozens of vectors per unit, one NVLink round trip after the other (measured:
+    // 60 us for the 784-100-10 model on 8 CTAs): such launches leave the update to the kernel of
+    // its own, which sizes its grid for the slice (fused_used tells the caller).
+    auto enough_workers = [&](long long ctas) {
+        const long long slice_quads = ua.unit_elems / 4 / std::max(1, ua.nranks);
+        return slice_quads <= 8 * ctas * 32 * kUpdWarps;
+    };
     // output tile: 128 rows of H  x  BN columns of K, BN a multiple of 16, <= 256
     const int n_tiles = (K + 255) / 256;
     const int BN = ((K + n_tiles - 1) / n_tiles + 15) / 16 * 16;
@@ -1613,6 +1621,9 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
         if ((rc = opt_in_smem(gemm_mnmajor2_kernel, kSmemMNMajor2))) return rc;
         const long long items2 = (long long)m2 * n2 * ks;
         const int pairs = (int)std::min<long long>(items2, npairs);
+        if (ua.enabled && !enough_workers(2 * pairs)) ua.enabled = 0;
+        if (fused_used) *fused_used = ua.enabled != 0;
+        const int threads = ua.enabled ? kThreadsDw : kThreads;
         gemm_mnmajor2_kernel<<<2 * pairs, threads, kSmemMNMajor2, st>>>(
             tmA, tmB, gW1, ldg, H, K, m2, n2, kb_total, ks, BN2, sy, ua);
         CME_LAUNCH_CHECK();
@@ -1629,6 +1640,9 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
     sy.sblocks = (kb_total / ksplit >= 128) ? std::min(m_tiles, 4) : 1;
     const long long items = (long long)m_tiles * n_tiles * ksplit;
     const int grid = (int)std::min<long long>(items, cme::sm_count());
+    if (ua.enabled && !enough_workers(grid)) ua.enabled = 0;
+    if (fused_used) *fused_used = ua.enabled != 0;
+    const int threads = ua.enabled ? kThreadsDw : kThreads;
     gemm_mnmajor_kernel<<<grid, threads, kSmemMNMajor, st>>>(
         tmA, tmB, gW1, ldg, H, K, m_tiles, n_tiles, kb_total, BN, 512u, 0, ksplit, sy, ua);
     CME_LAUNCH_CHECK();
@@ -1679,9 +1693,12 @@ int cme_mlp_dw1_update(const CmeMlpPlan* p, int64_t rows, float lr, float reg, i
     upd::UpdateArgs ua;
     int rc = cme::make_update_args(p, lr, reg, indirect, &ua);
     if (rc) return rc;
-    return dw1_launch(p->dz1, p->xb, p->grads[p->rank], rows, p->D + 1, p->H, p->ldx, p->ldh, p->ldx,
-                      (uint32_t*)p->sync_scratch, p->pads_dev, p->nranks, p->unit_rows,
-                      p->pad_local + cme::kPadStatus, &ua, cme::as_stream(stream));
+    bool fused_used = false;
+    rc = dw1_launch(p->dz1, p->xb, p->grads[p->rank], rows, p->D + 1, p->H, p->ldx, p->ldh, p->ldx,
+                    (uint32_t*)p->sync_scratch, p->pads_dev, p->nranks, p->unit_rows,
+                    p->pad_local + cme::kPadStatus, &ua, cme::as_stream(stream), &fused_used);
+    if (rc || fused_used) return rc;
+    return cme_mlp_update_stream_ind(p, lr, reg, indirect, stream);      // small GEMM: update on its own grid
 }
 
 int cme_mlp_fwd2_tc(const void* A1, const void* W2c, const float* b2, const int32_t* labels,

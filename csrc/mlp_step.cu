@@ -117,8 +117,10 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
         if ((rc = cme_mlp_fwd2_tc_ind(p->a1, p->w2c, params + g.o_b2, labels, sa, p->dz2, p->dz2b, loss_sum, p->pred,
                                       grads + g.o_b2, scale, rows, g.H, g.ldh, g.C, stream))) return rc;
     }
+    // the slot-wise (bit-reproducible) dW2 costs one more small launch: only where the rest of the
+    // step is reproducible too, i.e. with the one-kernel forward
     if ((rc = cme_mlp_bwd_tail_det(p->a1, p->dz2b, p->w2t, p->dz1, grads + g.o_w2, g.H, rows, g.H, g.ldh, g.C,
-                                   p->dw2_scratch, stream))) return rc;
+                                   need_zero ? nullptr : p->dw2_scratch, stream))) return rc;
     if (p->overlap) {
         // ONE kernel: the dW1 GEMM with the update warps inside it
         if ((rc = cme_mlp_dw1_update(p, rows, lr, reg, sa != nullptr, stream))) return rc;
