@@ -27,6 +27,32 @@ def create_mats(M, N, K):
     return A, B, C
 
 
+def reference_mygemm_seconds(M, N, K):
+    """Wall time of NUM_ITERS calls of the reference's myGEMM (ref fpcode/gpu_func.cu:259-297) through
+    baseline/harness.cpp::ref_mygemm, or None when the reference sources are not on this box."""
+    try:
+        import ctypes as C
+        import sys
+        from pathlib import Path
+
+        root = Path(__file__).resolve().parents[2]
+        if str(root) not in sys.path:
+            sys.path.insert(0, str(root))
+        from baseline.build_ref import build
+
+        lib_path = build()
+        if lib_path is None:
+            return None
+        lib = C.CDLL(str(lib_path))
+        lib.ref_mygemm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        sec = C.c_double(0)
+        if lib.ref_mygemm(M, N, K, NUM_ITERS, C.byref(sec)) != 0:
+            return None
+        return sec.value
+    except Exception:  # noqa: BLE001 - the comparison is optional
+        return None
+
+
 def test_gemm_fp64(M, N, K, alpha=2.0, beta=5.0, log=print) -> bool:
     A, B, C0 = create_mats(M, N, K)
     colmajor = lambda t: t.T.contiguous().cuda()          # noqa: E731
@@ -36,7 +62,9 @@ def test_gemm_fp64(M, N, K, alpha=2.0, beta=5.0, log=print) -> bool:
     ref = C0.cuda().clone()
 
     def lib_call():
-        ref.copy_(alpha * (Ag @ Bg) + beta * ref)
+        # ONE cuBLAS DGEMM with alpha and beta, like cublasDgemm in the reference
+        # (ref tests.cpp:176-199); no extra elementwise kernels in the timed region
+        torch.addmm(ref, Ag, Bg, beta=beta, alpha=alpha, out=ref)
 
     def own_call():
         dev.dgemm(False, False, M, N, K, alpha, dA, M, dB, K, beta, c_own, M)
@@ -65,6 +93,9 @@ def test_gemm_fp64(M, N, K, alpha=2.0, beta=5.0, log=print) -> bool:
     log(f"*** GEMM ({M},{N},{K}) ***")
     log(f"Time for reference GEMM implementation: {t_lib:.6f} seconds")
     log(f"Time for my GEMM implementation: {t_own:.6f} seconds")
+    t_ref = reference_mygemm_seconds(M, N, K)
+    if t_ref is not None:
+        log(f"Time for the reference's own myGEMM (rebuilt for sm_100, {NUM_ITERS} calls): {t_ref:.6f} seconds")
     log(f"Relative Inf error = {rel:.3e}  ->  {'PASSED' if ok else 'FAILED'}")
     return ok
 
