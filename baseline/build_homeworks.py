@@ -1,6 +1,6 @@
 """Builds the reference's homework programs unmodified for sm_100 (same-box baselines for the
 secondary metrics): `python -m baseline.build_homeworks`.  Sources are copied verbatim into
-baseline/_ref/hw{2,3}code (git-ignored); only the architecture flag differs from their Makefiles
+baseline/_ref/hw{2,3,4}code (git-ignored); only the architecture flag differs from their Makefiles
 (-arch=sm_20 -> -arch=sm_100, ref hw2code/Makefile:2, hw3code/Makefile:3-5)."""
 from __future__ import annotations
 
@@ -24,7 +24,7 @@ def run(cmd, cwd):
 def build() -> dict:
     out = {}
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    for hw in ("hw2code", "hw3code"):
+    for hw in ("hw2code", "hw3code", "hw4code"):
         if (REF / hw).exists():
             shutil.copytree(REF / hw, DST / hw, dirs_exist_ok=True)
     flags = ["-O3", "-arch=sm_100", "-w"]
@@ -34,6 +34,11 @@ def build() -> dict:
         out["hw2_q2"] = run([nvcc, *flags, "-I", "common", "main_q2.cu", "-o", "main_q2"], hw2)
     if hw3.exists():
         out["hw3"] = run([nvcc, *flags, "main.cu", "simParams.cpp", "Grid.cu", "-o", "main"], hw3)
+    hw4 = DST / "hw4code"
+    if hw4.exists():
+        # thrust::count_if is no longer included transitively (ref create_cipher.cu:192): force the header
+        out["hw4_create"] = run([nvcc, *flags, "-include", "thrust/count.h", "create_cipher.cu", "-o", "create_cipher"], hw4)
+        out["hw4_solve"] = run([nvcc, *flags, "solve_cipher.cu", "-o", "solve_cipher"], hw4)
     return out
 
 
