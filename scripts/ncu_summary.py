@@ -15,6 +15,7 @@ WANT = [
     ("dram__bytes_write.sum", "DRAM write"),
     ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM throughput % of peak"),
     ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor pipe active %"),
+    ("smsp__inst_executed.sum", "warp instructions"),
     ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "L2 throughput % of peak"),
     ("lts__t_sector_hit_rate.pct", "L2 hit rate %"),
     ("l1tex__m_xbar2l1tex_read_bytes.sum", "L2->SM bytes"),
@@ -37,7 +38,9 @@ def read(rep):
 
 
 def main():
-    reps = sorted((ROOT / "gpurun_out").glob("prof_*.ncu-rep"))
+    src = Path(sys.argv[1]) if len(sys.argv) > 1 else ROOT / "gpurun_out"
+    dst = Path(sys.argv[2]) if len(sys.argv) > 2 else ROOT / "profiles" / "ncu_summary.md"
+    reps = sorted(src.glob("prof_*.ncu-rep"))
     lines = ["# ncu summaries (ncu --set full --clock-control none, one instance per kernel)", "",
              f"Measured peaks used for fractions: HBM {peaks.get('hbm_gbs')} GB/s, bf16 "
              f"{peaks.get('bf16_tflops')} TFLOP/s burst / {peaks.get('bf16_tflops_sustained')} sustained.", ""]
@@ -52,8 +55,8 @@ def main():
                 v, u = d[key]
                 lines.append(f"| {label} | {v} {u} |")
         lines.append("")
-    (ROOT / "profiles").mkdir(exist_ok=True)
-    (ROOT / "profiles" / "ncu_summary.md").write_text("\n".join(lines))
+    dst.parent.mkdir(parents=True, exist_ok=True)
+    dst.write_text("\n".join(lines))
     print("\n".join(lines))
 
 
