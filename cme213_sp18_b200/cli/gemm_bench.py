@@ -89,12 +89,16 @@ def test_gemm_fp64(M, N, K, alpha=2.0, beta=5.0, log=print) -> bool:
     e1.record()
     torch.cuda.synchronize()
     t_own = e0.elapsed_time(e1) * 1e-3
+    c_simt = colmajor(C0)
+    t_simt = time_cuda_ms(lambda: dev.dgemm(False, False, M, N, K, alpha, dA, M, dB, K, beta, c_simt, M, simt=True),
+                          warmup=1, iters=NUM_ITERS) * NUM_ITERS * 1e-3
     got = c_own.T
     rel = float(((got - ref).abs().sum(dim=1).max() / ref.abs().sum(dim=1).max()).item())
     ok = rel <= GEMM_TOL
     log(f"*** GEMM ({M},{N},{K}) ***")
     log(f"Time for reference GEMM implementation: {t_lib:.6f} seconds")
-    log(f"Time for my GEMM implementation: {t_own:.6f} seconds")
+    log(f"Time for my GEMM implementation: {t_own:.6f} seconds  "
+        f"({2.0 * M * N * K * NUM_ITERS / t_own / 1e12:.1f} TFLOP/s fp64, DMMA; the round-1 CUDA-core kernel: {t_simt:.6f} s)")
     t_ref = reference_mygemm_seconds(M, N, K)
     if t_ref == "faulted":
         log("The reference's own myGEMM (rebuilt for sm_100) faulted on this shape: its kernels read out of "

@@ -304,7 +304,10 @@ class MLPEngineFP64:
     Buffers are column-major like the reference's device_cache; a column-major M x N matrix is
     held as a contiguous torch tensor of shape [N, M]."""
 
-    def __init__(self, H, max_rows: int, info: DistInfo | None = None):
+    def __init__(self, H, max_rows: int, info: DistInfo | None = None, comm: str = "fused",
+                 timeout_ms: int | None = None):
+        """comm: "fused" = one kernel per step does the gradient all-reduce, L2 and SGD over peer
+        memory (cme_allreduce_sgd_f64); "nccl" = dist.all_reduce + local SGD kernels (baseline)."""
         self.info = info or DistInfo(device=torch.device("cuda", torch.cuda.current_device()))
         self.D, self.Hh, self.C = H
         self.max_rows = max_rows
@@ -313,8 +316,20 @@ class MLPEngineFP64:
         self.sizes = [Hh * D, Hh, C * Hh, C]
         self.offs = [0, Hh * D, Hh * D + Hh, Hh * D + Hh + C * Hh]
         n = sum(self.sizes)
-        self.params = torch.zeros(n, dtype=f, device=d)
-        self.grads = torch.zeros(n, dtype=f, device=d)
+        self.n_pad = n + (n & 1)                  # the update kernel moves pairs of doubles
+        self.comm = ("nccl" if comm == "nccl" else "fused") if self.info.world > 1 else "local"
+        self.timeout_ms = int(timeout_ms if timeout_ms is not None else os.environ.get("CME_PEER_TIMEOUT_MS", 20000))
+        if self.comm == "nccl":
+            self.params = torch.zeros(self.n_pad, dtype=f, device=d)
+            self.grads = torch.zeros(self.n_pad, dtype=f, device=d)
+        else:
+            self._params = SymmetricTensor(self.n_pad, f, self.info)
+            self._grads = SymmetricTensor(self.n_pad, f, self.info)
+            self._pads = SymmetricTensor(dev.PAD_WORDS, torch.int32, self.info)
+            self._pads_dev = self._pads.ptr_table_dev()
+            self.params, self.grads = self._params.tensor, self._grads.tensor
+            if self.info.world > 1:
+                dist.barrier()                    # every rank's pad is zeroed before anyone signals
         self.x = torch.zeros((max_rows, D), dtype=f, device=d)
         self.a1 = torch.zeros((max_rows, Hh), dtype=f, device=d)
         self.da1 = torch.zeros((max_rows, Hh), dtype=f, device=d)
@@ -333,9 +348,12 @@ class MLPEngineFP64:
         self._seg(self.params, 1).copy_(nn.b[0].to(d))
         self._seg(self.params, 2).copy_(nn.W[1].T.contiguous().view(-1).to(d))
         self._seg(self.params, 3).copy_(nn.b[1].to(d))
+        torch.cuda.synchronize()
+        if self.info.world > 1:
+            dist.barrier()                        # no peer's update may land before this copy
 
     def store_params(self, nn) -> None:
-        torch.cuda.synchronize()
+        self.check_health()
         D, Hh, C = self.D, self.Hh, self.C
         nn.W[0] = self._seg(self.params, 0).view(D, Hh).T.contiguous().cpu()
         nn.b[0] = self._seg(self.params, 1).clone().cpu()
@@ -363,10 +381,23 @@ class MLPEngineFP64:
         dev.d_row_sum(self.dz1, gb1, Hh, rows)
 
     def update(self, lr: float, reg: float) -> None:
-        if self.info.world > 1:
-            dist.all_reduce(self.grads)             # parity path: library all-reduce
-        for i, r in ((0, reg), (1, 0.0), (2, reg), (3, 0.0)):
-            dev.d_sgd(self._seg(self.params, i), self._seg(self.grads, i), lr, r)
+        if self.comm == "nccl":
+            dist.all_reduce(self.grads)             # baseline: library all-reduce + four SGD kernels
+            for i, r in ((0, reg), (1, 0.0), (2, reg), (3, 0.0)):
+                dev.d_sgd(self._seg(self.params, i), self._seg(self.grads, i), lr, r)
+            return
+        dev.allreduce_sgd_f64(self._grads.peer_ptrs, self._params.peer_ptrs, self._pads_dev, self.info.rank,
+                              self.n_pad, self.offs[1], self.offs[2], self.offs[3], lr, reg, self.timeout_ms)
+
+    def check_health(self) -> None:
+        """Raises if a cross-GPU wait of the update kernel expired.  Synchronises the device."""
+        if self.comm == "nccl":
+            return
+        torch.cuda.synchronize(self.info.device)
+        st = int(self._pads.tensor[dev.F64_STATUS_WORD].item())
+        if st:
+            raise NativeError(f"rank {self.info.rank}: fp64 update timed out after {self.timeout_ms} ms "
+                              f"waiting for rank {st - 1}; the replicas are no longer consistent")
 
     def step(self, x: torch.Tensor, labels: torch.Tensor, rows: int, lr: float, reg: float,
              norm: float, want_loss: bool = False) -> None:

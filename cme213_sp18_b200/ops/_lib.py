@@ -43,6 +43,7 @@ _DEV_SIGS = {
     "cme_radix_scratch_bytes": [c_size_t],
     "cme_radix_sort": [P, P, c_size_t, P, c_size_t, P],
     "cme_dgemm": [c_int, c_int, c_int, c_int, c_int, c_double, P, c_int, P, c_int, c_double, P, c_int, P],
+    "cme_dgemm_simt": [c_int, c_int, c_int, c_int, c_int, c_double, P, c_int, P, c_int, c_double, P, c_int, P],
     "cme_d_bias_sigmoid": [P, P, c_int, c_int, P],
     "cme_d_bias_softmax_ce": [P, P, P, P, c_double, P, c_int, c_int, P],
     "cme_d_dsigmoid": [P, P, P, c_size_t, P],
@@ -63,6 +64,7 @@ _DEV_SIGS = {
     "cme_gemm_bf16": [P, P, P, c_i64, c_int, c_int, c_int, c_int, c_int, P],
     "cme_allreduce_sgd": [P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
+    "cme_allreduce_sgd_f64": [P, P, P, c_int, c_int, c_i64, c_i64, c_i64, c_i64, c_double, c_double, c_int, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_mlp_dw1_scratch_bytes": [],
     "cme_mlp_bwd_tail_scratch_floats": [c_int],

@@ -196,12 +196,14 @@ def radix_sort(keys: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------ fp64 parity path
 def dgemm(transA: bool, transB: bool, M: int, N: int, K: int, alpha: float, A: torch.Tensor, lda: int,
-          B: torch.Tensor, ldb: int, beta: float, Cm: torch.Tensor, ldc: int) -> None:
-    """Column-major C = alpha*op(A)*op(B) + beta*C (ref fpcode/gpu_func.cu:259-297)."""
+          B: torch.Tensor, ldb: int, beta: float, Cm: torch.Tensor, ldc: int, simt: bool = False) -> None:
+    """Column-major C = alpha*op(A)*op(B) + beta*C (ref fpcode/gpu_func.cu:259-297) on the fp64
+    tensor path (DMMA); simt=True runs the round-1 CUDA-core kernel (A/B timing only)."""
     require_cuda(A, B, Cm)
     assert A.dtype == B.dtype == Cm.dtype == torch.float64
-    check(device_lib().cme_dgemm(int(transA), int(transB), M, N, K, alpha, ptr(A), lda, ptr(B), ldb,
-                                 beta, ptr(Cm), ldc, stream_ptr()), "cme_dgemm")
+    fn = device_lib().cme_dgemm_simt if simt else device_lib().cme_dgemm
+    check(fn(int(transA), int(transB), M, N, K, alpha, ptr(A), lda, ptr(B), ldb, beta, ptr(Cm), ldc, stream_ptr()),
+          "cme_dgemm")
     _count()
 
 
@@ -382,6 +384,19 @@ def allreduce_sgd_mc(mc_grads: int, local_params: int, mc_params: int, mc_w1c: i
     check(device_lib().cme_allreduce_sgd_mc(mc_grads, local_params, mc_params, mc_w1c, rank, nranks,
                                             n_total, n_w1, ldx, kreg, w2_begin, w2_end, lr, reg,
                                             *(rng or (0, n_total)), stream_ptr()), "cme_allreduce_sgd_mc")
+    _count()
+
+
+F64_STATUS_WORD = 6 * 64 + 61     # pad word the fp64 update leaves its timeout code in
+
+
+def allreduce_sgd_f64(grad_ptrs, param_ptrs, pads_dev: torch.Tensor, rank: int, n: int, w1_end: int,
+                      w2_begin: int, w2_end: int, lr: float, reg: float, timeout_ms: int = 0) -> None:
+    """fp64 gradient all-reduce + L2 + SGD with its own peer handshake, one launch
+    (ref fpcode/neural_network.cpp:496-541 at the reference's precision)."""
+    check(device_lib().cme_allreduce_sgd_f64(_ptr_table(grad_ptrs), _ptr_table(param_ptrs), ptr(pads_dev),
+                                             rank, len(grad_ptrs), n, w1_end, w2_begin, w2_end, lr, reg,
+                                             timeout_ms, stream_ptr()), "cme_allreduce_sgd_f64")
     _count()
 
 

@@ -107,7 +107,7 @@ class DataParallelTrainer:
         if precision == "bf16":
             self.engine = MLPEngineBF16(H, self.max_rows, info, comm=comm)
         elif precision == "fp64":
-            self.engine = MLPEngineFP64(H, self.max_rows, info)
+            self.engine = MLPEngineFP64(H, self.max_rows, info, comm=comm)
         else:
             raise ValueError("precision must be 'bf16' or 'fp64'")
         self.data = None

@@ -98,6 +98,8 @@ allreduce_sgd_mc_kernel(const float* __restrict__ mc_grads, float* __restrict__ 
 // epoch == 0: use (and advance) the device-side call counter kept in slot 63 of
 // this rank's own channel row, so the launch has no per-call host argument and
 // can be captured in a CUDA graph.
+constexpr unsigned long long kBarrierTimeoutNs = 30ull * 1000000000ull;
+
 __global__ void peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank, int nranks,
                                     int channel, uint32_t epoch, int do_signal, int do_wait) {
     __shared__ uint32_t target;
@@ -121,10 +123,21 @@ __global__ void peer_barrier_kernel(uint32_t* const* __restrict__ pads, int rank
     if (do_wait) {
         const uint32_t* mine = pads[rank] + channel * 64 + r;
         const uint32_t want = target;
-        uint32_t v;
-        do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-        } while ((int32_t)(v - want) < 0);
+        // bounded: a peer that died would otherwise leave this GPU spinning for good.  After
+        // kBarrierTimeoutNs the kernel traps, and the host sees a launch failure at its next
+        // synchronisation instead of a hang.
+        const unsigned long long t0 = cme::global_timer_ns();
+        uint32_t v = cme::ld_relaxed_sys(mine);
+        while ((int32_t)(v - want) < 0) {
+            __nanosleep(100);
+            v = cme::ld_relaxed_sys(mine);
+            if (cme::global_timer_ns() - t0 > kBarrierTimeoutNs) {
+                printf("cme_peer_barrier: rank %d waited %llu s for rank %d on channel %d (epoch %u, saw %u)\n",
+                       rank, kBarrierTimeoutNs / 1000000000ull, r, channel, want, v);
+                __trap();
+            }
+        }
+        cme::fence_acquire_sys();
     }
 }
 
@@ -151,6 +164,94 @@ __global__ void __launch_bounds__(kUpdateThreads)
 update_stream_kernel(const __grid_constant__ upd::UpdateArgs a) {
     __shared__ uint32_t s_ok;
     upd::run_update(a, blockIdx.x, gridDim.x, threadIdx.x, kUpdateThreads, 1, &s_ok);
+}
+
+// ---- fp64 parity engine: gradient all-reduce + L2 + SGD, handshake included ----------------
+// One launch per step, no barrier launches around it.  Channel 6 of the pad carries "rank r's
+// gradients of step e are complete", channel 7 "rank r has written its slice of step e to every
+// replica"; slot 63 of channel 6 is this rank's step counter, slot 62 the CTA counter, slot 61
+// the status word (0, or 1 + the rank that never showed up).  Every rank reduces 1/nranks of the
+// vector in fixed rank order and stores the new parameters into every replica, so the replicas
+// are bit-identical and a run is reproducible.
+// Replaces D2H + MPI_Allreduce x4 + host SGD + H2D (ref fpcode/neural_network.cpp:496-541) at
+// the reference's own precision.
+struct PeerPtrsD {
+    double* grads[kMaxRanks];
+    double* params[kMaxRanks];
+};
+constexpr int kF64Ready = 6 * 64, kF64Done = 7 * 64;
+constexpr int kF64Epoch = kF64Ready + 63, kF64Ctr = kF64Ready + 62, kF64Status = kF64Ready + 61;
+
+__device__ __forceinline__ double2 ld_peer_d2(const double* p) {
+    double2 r;
+    asm volatile("ld.global.relaxed.sys.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p) : "memory");
+    return r;
+}
+
+__global__ void __launch_bounds__(256)
+allreduce_sgd_f64_kernel(PeerPtrsD pp, uint32_t* const* __restrict__ pads, int rank, int nranks, int64_t n,
+                         int64_t w1_end, int64_t w2_begin, int64_t w2_end, double lr, double reg,
+                         unsigned long long timeout_ns) {
+    __shared__ uint32_t s_epoch, s_ok, s_last;
+    uint32_t* pad = pads[rank];
+    if (threadIdx.x == 0) {
+        s_epoch = cme::ld_relaxed_gpu(pad + kF64Epoch) + 1;
+        s_ok = 1;
+        s_last = 0;
+    }
+    __syncthreads();
+    const uint32_t e = s_epoch;
+    if (blockIdx.x == 0 && threadIdx.x < nranks) {
+        // the kernels that wrote this rank's gradients ran before this one in the stream
+        __threadfence_system();
+        cme::red_relaxed_sys_add(pads[threadIdx.x] + kF64Ready + rank, 1u);
+    }
+    if (threadIdx.x < nranks && !upd::wait_flag_sys(pad + kF64Ready + threadIdx.x, e, timeout_ns)) {
+        pad[kF64Status] = 1u + threadIdx.x;
+        s_ok = 0;
+    }
+    __syncthreads();
+    if (s_ok) {
+        const int64_t pairs = n / 2;
+        const int64_t b = pairs * rank / nranks * 2, end = pairs * (rank + 1) / nranks * 2;
+        const int64_t gstride = (int64_t)gridDim.x * blockDim.x * 2;
+        for (int64_t i = b + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < end; i += gstride) {
+            double2 s = ld_peer_d2(pp.grads[0] + i);
+            for (int r = 1; r < nranks; ++r) {
+                const double2 g = ld_peer_d2(pp.grads[r] + i);
+                s.x += g.x;
+                s.y += g.y;
+            }
+            const double2 p = *reinterpret_cast<const double2*>(pp.params[rank] + i);
+            const double r0 = (i < w1_end || (i >= w2_begin && i < w2_end)) ? reg : 0.0;
+            const double r1 = (i + 1 < w1_end || (i + 1 >= w2_begin && i + 1 < w2_end)) ? reg : 0.0;
+            double2 q;
+            q.x = p.x - lr * (s.x + r0 * p.x);
+            q.y = p.y - lr * (s.y + r1 * p.y);
+            for (int r = 0; r < nranks; ++r) *reinterpret_cast<double2*>(pp.params[r] + i) = q;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        s_last = atomicAdd(pad + kF64Ctr, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    // last CTA of this rank: every slice of mine is written; tell every rank, and leave only when
+    // every rank has said the same (the next kernel may read the parameters and overwrite the
+    // gradients)
+    if (threadIdx.x < nranks) {
+        __threadfence_system();
+        cme::red_relaxed_sys_add(pads[threadIdx.x] + kF64Done + rank, 1u);
+        if (!upd::wait_flag_sys(pad + kF64Done + threadIdx.x, e, timeout_ns)) pad[kF64Status] = 1u + threadIdx.x;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        pad[kF64Ctr] = 0;
+        pad[kF64Epoch] = e;
+        __threadfence();
+    }
 }
 
 int slice_bounds(int64_t r_begin, int64_t r_end, int rank, int nranks, int64_t* b, int64_t* e) {
@@ -261,6 +362,33 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
     allreduce_sgd_mc_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
         mc_grads, local_params, mc_params, (__nv_bfloat16*)mc_w1c, b, e, n_w1, ldx, kreg, w2_begin,
         w2_end, lr, reg);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_allreduce_sgd_f64(double* const* grads_host, double* const* params_host, uint32_t* const* pads_dev,
+                          int rank, int nranks, int64_t n, int64_t w1_end, int64_t w2_begin, int64_t w2_end,
+                          double lr, double reg, int timeout_ms, void* stream) {
+    CME_CHECK_ARG(grads_host && params_host && pads_dev, "cme_allreduce_sgd_f64: null pointer table");
+    CME_CHECK_ARG(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks,
+                  "cme_allreduce_sgd_f64: rank %d of %d", rank, nranks);
+    CME_CHECK_ARG(n > 0 && n % 2 == 0, "cme_allreduce_sgd_f64: the vector must hold an even number of doubles (n = %lld)",
+                  (long long)n);
+    CME_CHECK_ARG(0 <= w1_end && w1_end <= w2_begin && w2_begin <= w2_end && w2_end <= n,
+                  "cme_allreduce_sgd_f64: bad segment bounds");
+    PeerPtrsD pp;
+    for (int r = 0; r < nranks; ++r) {
+        pp.grads[r] = grads_host[r];
+        pp.params[r] = params_host[r];
+        CME_CHECK_ARG(pp.grads[r] && pp.params[r], "cme_allreduce_sgd_f64: null peer %d", r);
+        CME_CHECK_ARG(((uintptr_t)pp.grads[r] | (uintptr_t)pp.params[r]) % 16 == 0,
+                      "cme_allreduce_sgd_f64: buffers of rank %d are not 16-byte aligned", r);
+    }
+    const int64_t slice_pairs = std::max<int64_t>(1, n / 2 / nranks);
+    const int grid = (int)std::min<int64_t>(cme::sm_count(), (slice_pairs + 255) / 256);
+    allreduce_sgd_f64_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
+        pp, pads_dev, rank, nranks, n, w1_end, w2_begin, w2_end, lr, reg,
+        (unsigned long long)(timeout_ms > 0 ? timeout_ms : 20000) * 1000000ull);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -1,13 +1,22 @@
 // fp64 parity path (ref fpcode/gpu_func.cu).
 //
 // The reference trains in fp64 end to end and grades the parallel run against
-// the serial one at 1e-7, and tcgen05 has no fp64 kind, so grade mode keeps an
-// fp64 SIMT path: one register-tiled GEMM that covers all four transpose cases
-// of the reference's myGEMM contract (ref gpu_func.cu:259-297 dispatches to
-// three 32x32 one-output-per-thread kernels), with guarded loads on every edge
-// (the reference read out of bounds in M/N on edge tiles, ref gpu_func.cu:108-124),
-// and fused elementwise kernels: bias+sigmoid, bias+softmax+cross-entropy
-// gradient, sigmoid derivative, row sums, SGD.
+// the serial one at 1e-7.  tcgen05 has no fp64 kind, so the fp64 tensor path of
+// this chip is the warp-level DMMA (mma.sync.m8n8k4.f64); the GEMM below is built
+// on it and covers all four transpose cases of the reference's myGEMM contract
+// (ref gpu_func.cu:259-297 dispatches to three 32x32 one-output-per-thread
+// kernels), with guarded loads on every edge (the reference read out of bounds
+// in M/N on edge tiles, ref gpu_func.cu:108-124):
+//   dgemm_mma_kernel     128x128 or 64x64 block tiles, 8 warps, operands through shared
+//                        memory with the next k-block prefetched into registers
+//   dgemm_skinny_kernel  min(M, N) <= 16 (layer 2, dW2, the -g 4 (800,10,1000) shape):
+//                        64x16 tiles, the K dimension split over the 8 warps of a CTA and
+//                        over a cluster of up to 8 CTAs, partial tiles summed through
+//                        (distributed) shared memory in a fixed order, so the result is
+//                        reproducible and needs no workspace and no atomics
+//   dgemm_kernel         the round-1 CUDA-core kernel, kept as cme_dgemm_simt for A/B timing
+// Fused elementwise kernels: bias+sigmoid, bias+softmax+cross-entropy gradient, sigmoid
+// derivative, row sums, SGD.
 #include "common.cuh"
 
 namespace {
@@ -80,6 +89,218 @@ dgemm_kernel(int M, int N, int K, double alpha, const double* __restrict__ A, in
             *c = (beta == 0.0) ? alpha * acc[i][j] : alpha * acc[i][j] + beta * (*c);
         }
     }
+}
+
+// ---- DMMA ------------------------------------------------------------------------------------
+// D(8x8) += A(8x4) * B(4x8).  Lane l: g = l / 4, t = l % 4 holds A(g, t), B(t, g), D(g, 2t), D(g, 2t+1).
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+constexpr int MK = 16;   // k-block of the shared-memory kernel
+
+// 8 warps as 4 (M) x 2 (N); a warp owns (BM/4) x (BN/2) of the block tile as m8n8 fragments.
+// Shared layouts keep the dimension that is contiguous in global memory contiguous in shared
+// memory (conflict-free stores), with row strides chosen so that a fragment read (8 values of g,
+// 4 values of t) touches 32 distinct 8-byte words in two wavefronts:
+//   [k][m] rows of BM + 8 doubles (stride = 8 mod 16),  [m][k] rows of MK + 4 doubles (stride = 4 mod 16)
+template <int BM_, int BN_, bool TA, bool TB>
+__global__ void __launch_bounds__(256, (BM_ == 64 ? 2 : 1))
+dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A, int lda,
+                 const double* __restrict__ B, int ldb, double beta, double* __restrict__ C, int ldc) {
+    constexpr int SA = TA ? MK + 4 : BM_ + 8;
+    constexpr int SB = TB ? BN_ + 8 : MK + 4;
+    constexpr int AE = BM_ * MK / 256, BE = BN_ * MK / 256;
+    constexpr int WM = BM_ / 4, WN = BN_ / 2, MT = WM / 8, NT = WN / 8;
+    __shared__ double As[TA ? BM_ * SA : MK * SA];
+    __shared__ double Bs[TB ? MK * SB : BN_ * SB];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int m0 = blockIdx.x * BM_, n0 = blockIdx.y * BN_;
+    const int wm0 = (warp & 3) * WM, wn0 = (warp >> 2) * WN;
+    double acc[MT][NT][2];
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    double ra[AE], rb[BE];
+
+    auto gload = [&](int k0) {
+#pragma unroll
+        for (int x = 0; x < AE; ++x) {
+            const int e = tid + x * 256;
+            const int m = TA ? e / MK : e % BM_, k = TA ? e % MK : e / BM_;
+            const int gm = m0 + m, gk = k0 + k;
+            ra[x] = (gm < M && gk < K) ? (TA ? A[(size_t)gk + (size_t)lda * gm] : A[(size_t)gm + (size_t)lda * gk]) : 0.0;
+        }
+#pragma unroll
+        for (int x = 0; x < BE; ++x) {
+            const int e = tid + x * 256;
+            const int n = TB ? e % BN_ : e / MK, k = TB ? e / BN_ : e % MK;
+            const int gn = n0 + n, gk = k0 + k;
+            rb[x] = (gn < N && gk < K) ? (TB ? B[(size_t)gn + (size_t)ldb * gk] : B[(size_t)gk + (size_t)ldb * gn]) : 0.0;
+        }
+    };
+
+    gload(0);
+    for (int k0 = 0; k0 < K; k0 += MK) {
+#pragma unroll
+        for (int x = 0; x < AE; ++x) {
+            const int e = tid + x * 256;
+            const int m = TA ? e / MK : e % BM_, k = TA ? e % MK : e / BM_;
+            As[TA ? m * SA + k : k * SA + m] = ra[x];
+        }
+#pragma unroll
+        for (int x = 0; x < BE; ++x) {
+            const int e = tid + x * 256;
+            const int n = TB ? e % BN_ : e / MK, k = TB ? e / BN_ : e % MK;
+            Bs[TB ? k * SB + n : n * SB + k] = rb[x];
+        }
+        __syncthreads();
+        if (k0 + MK < K) gload(k0 + MK);       // in flight while the tensor pipe works on this block
+#pragma unroll
+        for (int kk = 0; kk < MK; kk += 4) {
+            double a[MT], b[NT];
+            const int k = kk + t;
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+                const int m = wm0 + i * 8 + g;
+                a[i] = As[TA ? m * SA + k : k * SA + m];
+            }
+#pragma unroll
+            for (int j = 0; j < NT; ++j) {
+                const int n = wn0 + j * 8 + g;
+                b[j] = Bs[TB ? k * SB + n : n * SB + k];
+            }
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+                for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+        for (int x = 0; x < 2; ++x) {
+            const int gn = n0 + wn0 + j * 8 + 2 * t + x;
+            if (gn >= N) continue;
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+                const int gm = m0 + wm0 + i * 8 + g;
+                if (gm >= M) continue;
+                double* c = C + (size_t)gm + (size_t)ldc * gn;
+                // beta == 0 must not read C (it may hold NaNs from a fresh allocation)
+                *c = (beta == 0.0) ? alpha * acc[i][j][x] : alpha * acc[i][j][x] + beta * (*c);
+            }
+        }
+}
+
+// ---- skinny products ---------------------------------------------------------------------
+// C(i, j) = alpha * sum_k A(i, k) B(k, j) + beta * C(i, j) for i < I, j < J <= 16, all three
+// operands addressed through element strides (the host maps the transposes, and the M <= 16
+// case as the transposed product, onto them).  One cluster per 64 rows of i; CTA c of the
+// cluster and warp w of the CTA take the k-blocks of four q = (x * S + c) * 8 + w.  Fragments
+// come straight from global memory: every operand element is used once per cluster, and a
+// fragment load is eight 32-byte sectors, all of them used, whichever dimension is contiguous.
+constexpr int SK_I = 64, SK_J = 16, SK_LD = SK_I + 4;      // partial tile [j][i], rows of 68 doubles
+
+__device__ __forceinline__ double ld_dsmem_f64(const double* local, uint32_t cta) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(local);
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(cta));
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(ra) : "memory");
+    return v;
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(256)
+dgemm_skinny_kernel(int I, int J, int K, double alpha, const double* __restrict__ A, int64_t ai, int64_t ak,
+                    const double* __restrict__ B, int64_t bk, int64_t bj, double beta, double* __restrict__ C,
+                    int64_t ci, int64_t cj) {
+    __shared__ double red[4][SK_J * SK_LD];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int S = gridDim.x;                     // cluster = the CTAs of one row of the grid
+    const int cta = blockIdx.x;
+    const int i0 = blockIdx.y * SK_I;
+    double acc[8][2][2];
+#pragma unroll
+    for (int m = 0; m < 8; ++m)
+#pragma unroll
+        for (int n = 0; n < 2; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
+
+    const int nq = (K + 3) >> 2;
+    const bool j0_in = g < J, j1_in = 8 + g < J;
+#pragma unroll 2
+    for (int q = cta * 8 + warp; q < nq; q += S * 8) {
+        const int k = q * 4 + t;
+        const bool kin = k < K;
+        double a[8], b[2];
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+            const int i = i0 + m * 8 + g;
+            a[m] = (kin && i < I) ? A[(int64_t)i * ai + (int64_t)k * ak] : 0.0;
+        }
+        b[0] = (kin && j0_in) ? B[(int64_t)k * bk + (int64_t)g * bj] : 0.0;
+        b[1] = (kin && j1_in) ? B[(int64_t)k * bk + (int64_t)(8 + g) * bj] : 0.0;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+            dmma884(acc[m][0][0], acc[m][0][1], a[m], b[0]);
+            dmma884(acc[m][1][0], acc[m][1][1], a[m], b[1]);
+        }
+    }
+
+    // the 8 warps' partial tiles, added in a fixed order: (0+4, 1+5, 2+6, 3+7), (+2, +3), (+1)
+#pragma unroll
+    for (int half = 4; half >= 1; half >>= 1) {
+        if (warp >= half && warp < 2 * half) {
+            double* dst = red[warp - half];
+#pragma unroll
+            for (int m = 0; m < 8; ++m)
+#pragma unroll
+                for (int n = 0; n < 2; ++n)
+#pragma unroll
+                    for (int x = 0; x < 2; ++x) dst[(n * 8 + 2 * t + x) * SK_LD + m * 8 + g] = acc[m][n][x];
+        }
+        __syncthreads();
+        if (warp < half) {
+            const double* src = red[warp];
+#pragma unroll
+            for (int m = 0; m < 8; ++m)
+#pragma unroll
+                for (int n = 0; n < 2; ++n)
+#pragma unroll
+                    for (int x = 0; x < 2; ++x) acc[m][n][x] += src[(n * 8 + 2 * t + x) * SK_LD + m * 8 + g];
+        }
+        __syncthreads();
+    }
+    if (warp == 0) {
+#pragma unroll
+        for (int m = 0; m < 8; ++m)
+#pragma unroll
+            for (int n = 0; n < 2; ++n)
+#pragma unroll
+                for (int x = 0; x < 2; ++x) red[0][(n * 8 + 2 * t + x) * SK_LD + m * 8 + g] = acc[m][n][x];
+    }
+    __syncthreads();
+    if (S > 1) cluster_barrier();                // every CTA's tile is in its red[0]
+    if (cta == 0) {
+        for (int e = tid; e < SK_I * SK_J; e += 256) {
+            const int i = e % SK_I, j = e / SK_I;
+            const double* cell = &red[0][j * SK_LD + i];
+            double v = *cell;
+            for (int r = 1; r < S; ++r) v += ld_dsmem_f64(cell, (uint32_t)r);   // fixed order
+            if (i0 + i < I && j < J) {
+                double* c = C + (int64_t)(i0 + i) * ci + (int64_t)j * cj;
+                *c = (beta == 0.0) ? alpha * v : alpha * v + beta * (*c);
+            }
+        }
+    }
+    if (S > 1) cluster_barrier();                // nobody leaves while CTA 0 still reads its tile
 }
 
 __device__ __forceinline__ double sigmoid_d(double x) { return 1.0 / (1.0 + exp(-x)); }
@@ -170,15 +391,86 @@ axpby_kernel(double* __restrict__ c, const double* __restrict__ a, const double*
 
 }  // namespace
 
+namespace {
+
+int dgemm_check(int transA, int transB, int M, int N, int K, const double* A, int lda, const double* B, int ldb,
+                double* C, int ldc) {
+    CME_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "cme_dgemm: negative dimension");
+    if (M == 0 || N == 0) return 1;
+    CME_CHECK_ARG(A && B && C, "cme_dgemm: null matrix");
+    CME_CHECK_ARG(lda >= (transA ? K : M) && ldb >= (transB ? N : K) && ldc >= M,
+                  "cme_dgemm: leading dimension too small (lda=%d ldb=%d ldc=%d)", lda, ldb, ldc);
+    return 0;
+}
+
+template <int BM_, int BN_>
+int launch_mma(bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B,
+               int ldb, double beta, double* C, int ldc, cudaStream_t st) {
+    dim3 grid((M + BM_ - 1) / BM_, (N + BN_ - 1) / BN_);
+    CME_CHECK_ARG(grid.y < 65536, "cme_dgemm: N too large for one launch");
+    if (!ta && !tb) dgemm_mma_kernel<BM_, BN_, false, false><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+    else if (ta && !tb) dgemm_mma_kernel<BM_, BN_, true, false><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+    else if (!ta && tb) dgemm_mma_kernel<BM_, BN_, false, true><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+    else dgemm_mma_kernel<BM_, BN_, true, true><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_skinny(bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B,
+                  int ldb, double beta, double* C, int ldc, cudaStream_t st) {
+    // element strides of op(A)(m, k) and op(B)(k, n)
+    const int64_t am = ta ? lda : 1, ak = ta ? 1 : lda;
+    const int64_t bk = tb ? ldb : 1, bn = tb ? 1 : ldb;
+    int I, J;
+    const double *P, *Q;
+    int64_t pi, pk, qk, qj, ci, cj;
+    if (N <= SK_J) {            // tall C: rows of C are the long dimension
+        I = M, J = N, P = A, pi = am, pk = ak, Q = B, qk = bk, qj = bn, ci = 1, cj = ldc;
+    } else {                    // wide C: the transposed product, C^T = op(B)^T op(A)^T
+        I = N, J = M, P = B, pi = bn, pk = bk, Q = A, qk = ak, qj = am, ci = ldc, cj = 1;
+    }
+    // split K over a cluster while every warp keeps at least four k-blocks of four
+    int S = 1;
+    while (S < 8 && K >= 128 * 2 * S) S *= 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(S, (I + SK_I - 1) / SK_I, 1);
+    cfg.blockDim = dim3(256, 1, 1);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CME_CHECK_ARG(cfg.gridDim.y < 65536, "cme_dgemm: long dimension too large for one launch");
+    CME_CUDA(cudaLaunchKernelEx(&cfg, dgemm_skinny_kernel, I, J, K, alpha, P, pi, pk, Q, qk, qj, beta, C, ci, cj));
+    return 0;
+}
+
+}  // namespace
+
 extern "C" {
 
 int cme_dgemm(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
               const double* B, int ldb, double beta, double* C, int ldc, void* stream) {
-    CME_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "cme_dgemm: negative dimension");
-    if (M == 0 || N == 0) return 0;
-    CME_CHECK_ARG(A && B && C, "cme_dgemm: null matrix");
-    CME_CHECK_ARG(lda >= (transA ? K : M) && ldb >= (transB ? N : K) && ldc >= M,
-                  "cme_dgemm: leading dimension too small (lda=%d ldb=%d ldc=%d)", lda, ldb, ldc);
+    const int chk = dgemm_check(transA, transB, M, N, K, A, lda, B, ldb, C, ldc);
+    if (chk) return chk < 0 ? chk : 0;
+    cudaStream_t st = cme::as_stream(stream);
+    const bool ta = transA != 0, tb = transB != 0;
+    if (M <= SK_J || N <= SK_J) return launch_skinny(ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    // 128x128 tiles once they fill the machine; below that 64x64 tiles, two CTAs per SM
+    const int64_t big_tiles = (int64_t)((M + 127) / 128) * ((N + 127) / 128);
+    if (big_tiles >= cme::sm_count())
+        return launch_mma<128, 128>(ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    return launch_mma<64, 64>(ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+}
+
+/* The round-1 CUDA-core kernel (64x64 tiles, 4x4 outputs per thread), for A/B timing only. */
+int cme_dgemm_simt(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
+                   const double* B, int ldb, double beta, double* C, int ldc, void* stream) {
+    const int chk = dgemm_check(transA, transB, M, N, K, A, lda, B, ldb, C, ldc);
+    if (chk) return chk < 0 ? chk : 0;
     dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN);
     CME_CHECK_ARG(grid.y < 65536, "cme_dgemm: N too large for one launch");
     cudaStream_t st = cme::as_stream(stream);

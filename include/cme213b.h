@@ -138,6 +138,9 @@ int cme_radix_sort(uint32_t* keys, uint32_t* tmp, size_t n, void* scratch, size_
  * dimensions of op(A) (MxK), op(B) (KxN), C (MxN); lda/ldb/ldc leading dims. */
 int cme_dgemm(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
               const double* B, int ldb, double beta, double* C, int ldc, void* stream);
+/* The round-1 CUDA-core kernel behind the same contract, kept for A/B timing (cli/gemm_bench). */
+int cme_dgemm_simt(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
+              const double* B, int ldb, double beta, double* C, int ldc, void* stream);
 /* Fused fp64 MLP pieces, column-major like the reference's device_cache.
  * z is rows x cols (one sample per column). */
 int cme_d_bias_sigmoid(double* z, const double* bias, int rows, int cols, void* stream);
@@ -307,6 +310,16 @@ int cme_allreduce_sgd_mc(const float* mc_grads, float* local_params, float* mc_p
                          void* mc_w1c, int rank, int nranks, int64_t n_total, int64_t n_w1, int ldx,
                          int kreg, int64_t w2_begin, int64_t w2_end, float lr, float reg,
                          int64_t range_begin, int64_t range_end, void* stream);
+
+/* fp64 parity engine: gradient all-reduce + L2 + SGD in ONE launch that carries its own peer
+ * handshake (pad channels 6 and 7; no barrier launches).  grads/params: one pointer per rank
+ * (peer-mapped), n doubles each (n even, buffers 16-byte aligned).  reg applies to [0, w1_end)
+ * and [w2_begin, w2_end).  Every rank reduces 1/nranks of the vector in rank order and writes
+ * every replica.  Waits are bounded by timeout_ms (0 = 20 s); an expired wait leaves 1 + the
+ * missing rank in word 6*64+61 of this rank's pad. */
+int cme_allreduce_sgd_f64(double* const* grads_host, double* const* params_host, uint32_t* const* pads_dev,
+                          int rank, int nranks, int64_t n, int64_t w1_end, int64_t w2_begin, int64_t w2_end,
+                          double lr, double reg, int timeout_ms, void* stream);
 
 /* ---- native step executor ------------------------------------------------------
  * Every device buffer of one rank's bf16 engine.  D inputs, H hidden units, C classes;

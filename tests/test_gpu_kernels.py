@@ -118,7 +118,10 @@ def test_parity_and_radix(dev):
 
 # ------------------------------------------------------------------ fp64 GEMM (ref -g 4)
 @pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
-@pytest.mark.parametrize("mnk", [(800, 1000, 784), (800, 10, 1000), (37, 65, 19), (1, 1, 1)])
+@pytest.mark.parametrize("mnk", [(800, 1000, 784), (800, 10, 1000), (37, 65, 19), (1, 1, 1),
+                                 (10, 1000, 800),       # wide C: the skinny kernel on the transposed product
+                                 (2100, 2000, 70),      # enough 128 x 128 tiles to fill the machine
+                                 (16, 16, 300), (17, 9, 5), (1000, 100, 10)])
 def test_dgemm_rel_inf_norm(dev, ta, tb, mnk):
     M, N, K = mnk
     g = torch.Generator().manual_seed(M * 7 + N)
@@ -134,6 +137,13 @@ def test_dgemm_rel_inf_norm(dev, ta, tb, mnk):
     got = dC.cpu().T
     rel = (got - want).abs().sum(dim=1).max() / want.abs().sum(dim=1).max()
     assert rel <= 1e-12, float(rel)                          # ref GEMM_TOL
+    # every element, not only the norm: a misplaced fragment would hide in a norm of random data
+    scale = alpha * (A.abs().T if ta else A.abs()) @ (B.abs().T if tb else B.abs()) + beta * C0.abs()
+    assert ((got - want).abs() <= 1e-13 * scale + 1e-300).all()
+    # the k-split of the skinny kernel adds in a fixed order: a second call gives the same bits
+    dC2 = colmajor(C0)
+    dev.dgemm(ta, tb, M, N, K, alpha, dA, A.shape[0], dB, B.shape[0], beta, dC2, M)
+    assert torch.equal(dC, dC2)
 
 
 def test_dgemm_beta_zero_ignores_nan(dev):
