@@ -207,11 +207,15 @@ parallel_train(p2p, x, lab, 0.5, 1e-4, 2, 800, info=info, comm="p2p", data_mode=
 parallel_train(mc, x, lab, 0.5, 1e-4, 2, 800, info=info, comm="mc", data_mode="sharded")
 parallel_train(nccl, x, lab, 0.5, 1e-4, 2, 800, info=info, comm="nccl", data_mode="sharded")
 parallel_train(fp64, x, lab, 0.5, 1e-4, 2, 800, info=info, precision="fp64", data_mode="sharded")
+fp64n = base.clone()          # the same engine on the library all-reduce
+parallel_train(fp64n, x, lab, 0.5, 1e-4, 2, 800, info=info, precision="fp64", comm="nccl", data_mode="sharded")
 if info.rank == 0:
     ser = base.clone()
     M.train(ser, x, lab, 0.5, 1e-4, 2, 800)
     r1 = grading.check_nn_errors(ser, fp64, filename={str(tmp_path / 'e1.txt')!r}, log=lambda *_: None)
     assert r1["passed"], r1
+    for a, b in zip(fp64.W + fp64.b, fp64n.W + fp64n.b):
+        assert float((a - b).abs().max() / b.abs().max()) < 1e-11
     for name, got in (("fused", fused), ("p2p", p2p), ("mc", mc)):
         for a, b in zip(got.W + got.b, nccl.W + nccl.b):
             d = (a - b).abs().max() / b.abs().max()
