@@ -179,8 +179,14 @@ class MLPEngineBF16:
 
     # ---- one minibatch slice, piece by piece (tests, profiling, the baseline paths) ----
     def stage(self, x_u8_ptr: int, rows: int) -> None:
-        """uint8 pixels at x_u8_ptr (local or peer-mapped) -> bf16 rows + ones column."""
-        dev.u8_to_bf16_rows(x_u8_ptr, self.xb, rows, self.D, add_ones=True)
+        """uint8 pixels at x_u8_ptr (local or peer-mapped) -> bf16 rows + ones column; the same
+        launch refreshes the bf16 copies of W2 (the step executor does likewise, so whatever
+        runs a forward pass starts from the current W2)."""
+        if self.tail == "tc":
+            _, w2, _ = self._views(self.params.tensor)
+            dev.mlp_stage_recast(x_u8_ptr, self.xb, rows, self.D, w2, self.w2c, self.w2t, self.Hh, self.C)
+        else:
+            dev.u8_to_bf16_rows(x_u8_ptr, self.xb, rows, self.D, add_ones=True)
 
     def forward(self, rows: int, labels: torch.Tensor | None, scale: float, want_loss: bool = False,
                 want_grad: bool = True, skip_fwd1: bool = False) -> None:
@@ -227,8 +233,6 @@ class MLPEngineBF16:
                               self.D, w2_begin, w2_end, lr, reg)
         else:
             dev.mlp_update_stream(self.plan, lr, reg)
-        if self.tail == "tc":
-            self._recast_w2()
 
     def _step_body(self, x_u8_ptr: int, labels: torch.Tensor, rows: int, lr: float, reg: float,
                    norm: float, want_loss: bool) -> None:

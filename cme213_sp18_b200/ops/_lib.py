@@ -65,6 +65,7 @@ _DEV_SIGS = {
     "cme_allreduce_sgd": [P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_allreduce_sgd_mc": [P, P, P, P, c_int, c_int, c_i64, c_i64, c_int, c_int, c_i64, c_i64, c_float, c_float, c_i64, c_i64, P],
     "cme_allreduce_sgd_f64": [P, P, P, c_int, c_int, c_i64, c_i64, c_i64, c_i64, c_double, c_double, c_int, P],
+    "cme_mlp_stage_recast": [P, P, P, c_i64, c_int, c_int, P, P, c_int, P, c_int, c_int, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_mlp_dw1_scratch_bytes": [],
     "cme_mlp_bwd_tail_scratch_floats": [c_int],

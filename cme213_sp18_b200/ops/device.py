@@ -252,6 +252,15 @@ def u8_to_bf16_rows(src_ptr: int, dst: torch.Tensor, rows: int, cols: int, add_o
     _count()
 
 
+def mlp_stage_recast(src_ptr: int, dst: torch.Tensor, rows: int, cols: int, W2: torch.Tensor, w2c: torch.Tensor,
+                     w2t: torch.Tensor, H: int, C: int = 10) -> None:
+    """The staging launch of a step: uint8 rows -> bf16 rows + ones column, and in the same launch
+    the bf16 copies of W2 that layer 2 and the backward tail read."""
+    check(device_lib().cme_mlp_stage_recast(src_ptr, None, ptr(dst), rows, cols, dst.shape[1], ptr(W2), ptr(w2c),
+                                            w2c.shape[1], ptr(w2t), H, C, stream_ptr()), "cme_mlp_stage_recast")
+    _count()
+
+
 def mlp_fwd1(X: torch.Tensor, W1c: torch.Tensor, A1: torch.Tensor, rows: int, K: int, H: int) -> None:
     """A1 = sigmoid(X @ W1c.T) on tcgen05 (ref fpcode/neural_network.cpp:289-300)."""
     check(device_lib().cme_mlp_fwd1(ptr(X), ptr(W1c), None, ptr(A1), rows, K, H, X.shape[1],

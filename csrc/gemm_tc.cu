@@ -626,7 +626,9 @@ __device__ __forceinline__ void dw_publish(const DwSync& sy, uint32_t* ctr, int 
     if ((int)old + 1 == parts) {
         sy.unit_ctr[unit] = 0;
         if (sy.pads) {
-            __threadfence_system();                 // one fence, then the bumps (see red_relaxed_sys_add)
+            // one fence, then the bumps (see red_relaxed_sys_add); a single rank's readers are on this GPU
+            if (sy.nranks > 1) __threadfence_system();
+            else __threadfence();
             for (int r = 0; r < sy.nranks; ++r) cme::red_relaxed_sys_add(sy.pads[r] + cme::kPadUnit0 + unit, 1u);
         }
     }
@@ -1466,6 +1468,27 @@ int choose_ksplit(int tiles_mn, int kb_total, int sms) {
     return best;
 }
 
+// Small dW1 products (a handful of tiles): one SM pulls its operands out of L2 at ~100 GB/s, so a
+// k-block costs about c = 0.10 + 0.0018 * BN microseconds and every chained epilogue of the ordered
+// split-K about e = 0.9 + 0.009 * BN (fitted on the 784-100-10 model, 3200 rows: 34 us with one
+// 208-wide chunk per tile, 15 us with 64-wide tiles and 2-3 chunks).  Narrow tiles put more SMs
+// to work on the same bytes; pick the column-tile width and the k-split that minimise
+// c * ceil(kb / s) + e * s with every item resident at once.
+void choose_small_tiling(int m_tiles, int K, int kb_total, int sms, int* bn_cap, int* ksplit) {
+    double best = 1e30;
+    *bn_cap = 256, *ksplit = 1;
+    for (int cap : {64, 128, 256}) {
+        const int nt = (K + cap - 1) / cap;
+        const int bn = ((K + nt - 1) / nt + 15) / 16 * 16;
+        const double c = 0.10 + 0.0018 * bn, e = 0.9 + 0.009 * bn;
+        for (int s = 1; s <= 16 && (long long)m_tiles * nt * s <= sms; ++s) {
+            if (s > 1 && kb_total / s < 4) break;
+            const double t = c * ((kb_total + s - 1) / s) + e * s;
+            if (t < best - 1e-9) { best = t; *bn_cap = cap; *ksplit = s; }
+        }
+    }
+}
+
 uint32_t pow2_cols(int need) {
     uint32_t c = 32;
     while ((int)c < need) c <<= 1;
@@ -1566,18 +1589,24 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
     upd::UpdateArgs ua{};
     if (fused) ua = *fused;
     // The update warps are 128 threads per CTA of THIS grid.  A small GEMM (few CTAs) would leave
-    // each of them dozens of vectors per unit, one NVLink round trip after the other (measured:
+    // each of them many vectors per unit (more than four here), one NVLink round trip after the other (measured:
     // 60 us for the 784-100-10 model on 8 CTAs): such launches leave the update to the kernel of
     // its own, which sizes its grid for the slice (fused_used tells the caller).
     auto enough_workers = [&](long long ctas) {
         const long long slice_quads = ua.unit_elems / 4 / std::max(1, ua.nranks);
-        return slice_quads <= 8 * ctas * 32 * kUpdWarps;
+        return slice_quads <= 4 * ctas * 32 * kUpdWarps;
     };
     // output tile: 128 rows of H  x  BN columns of K, BN a multiple of 16, <= 256
-    const int n_tiles = (K + 255) / 256;
-    const int BN = ((K + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    static const int dev_bn = getenv("CME_DW1_BN") ? atoi(getenv("CME_DW1_BN")) : 0;      // tuning hooks
+    static const int dev_ks = getenv("CME_DW1_KS") ? atoi(getenv("CME_DW1_KS")) : 0;
     const int m_tiles = (H + BM - 1) / BM;
     const int kb_total = (int)((rows + BK - 1) / BK);
+    int bn_cap = 256, ks_small = 0;
+    if ((long long)m_tiles * ((K + 255) / 256) * 16 <= cme::sm_count())
+        choose_small_tiling(m_tiles, K, kb_total, cme::sm_count(), &bn_cap, &ks_small);
+    if (dev_bn >= 16 && dev_bn <= 256) bn_cap = dev_bn, ks_small = 0;
+    const int n_tiles = (K + bn_cap - 1) / bn_cap;
+    const int BN = ((K + n_tiles - 1) / n_tiles + 15) / 16 * 16;
     CUtensorMap tmA, tmB;
     int rc;
     if ((rc = make_map(&tmA, dZ1, (uint64_t)H, (uint64_t)rows, (uint64_t)ldh, 64, BK))) return rc;
@@ -1636,7 +1665,9 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
     sy.m_tiles = m_tiles;
     sy.sblocks = 1;                      // filled in below, once ksplit is known
     if ((rc = opt_in_smem(gemm_mnmajor_kernel, kSmemMNMajor))) return rc;
-    const int ksplit = choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
+    const int ksplit = dev_ks > 0 ? std::min(dev_ks, std::max(1, kb_total))
+                       : ks_small > 0 ? ks_small
+                                      : choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
     sy.sblocks = (kb_total / ksplit >= 128) ? std::min(m_tiles, 4) : 1;
     const long long items = (long long)m_tiles * n_tiles * ksplit;
     const int grid = (int)std::min<long long>(items, cme::sm_count());

@@ -28,15 +28,48 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
     return r;
 }
 
+// one thread per hidden unit: column h of W2 -> bf16 row entries of w2c and row h of w2t
+__device__ __forceinline__ void recast_w2_column(const float* __restrict__ W2, __nv_bfloat16* __restrict__ w2c, int ldh,
+                                                 __nv_bfloat16* __restrict__ w2t, int H, int C, int h) {
+    if (h >= H) return;
+    float v[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) v[c] = (c < C) ? W2[(size_t)c * H + h] : 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+        if (c < C) w2c[(size_t)c * ldh + h] = __float2bfloat16_rn(v[c]);
+    if (w2t) {
+        uint4* d = reinterpret_cast<uint4*>(w2t + (size_t)h * 64);
+        d[0] = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
+        d[1] = make_uint4(pack2(v[8], v[9]), pack2(v[10], v[11]), pack2(v[12], v[13]), pack2(v[14], v[15]));
+    }
+}
+
+// The bf16 copies of W2 ride in the staging launch of the NEXT step (blocks past `first_block`):
+// the update kernel that wrote W2 has finished by then, and a launch of its own cost ~4 us, a
+// tenth of a step of the 784-100-10 model.
+struct RecastArgs {
+    const float* W2;
+    __nv_bfloat16* w2c;
+    __nv_bfloat16* w2t;
+    int ldh, H, C;
+    int first_block;      // 0 = no recast in this launch
+};
+
 // ---- staging -------------------------------------------------------------------
 // one thread per 16-element chunk of a destination row
 __global__ void __launch_bounds__(256)
 u8_to_bf16_kernel(const uint8_t* __restrict__ src_arg, const CmeStepArgs* __restrict__ sa,
-                  __nv_bfloat16* __restrict__ dst, int64_t rows, int cols, int ld, int add_ones) {
+                  __nv_bfloat16* __restrict__ dst, int64_t rows, int cols, int ld, int add_ones, RecastArgs rc) {
+    if (rc.first_block && (int)blockIdx.x >= rc.first_block) {
+        recast_w2_column(rc.W2, rc.w2c, rc.ldh, rc.w2t, rc.H, rc.C,
+                         ((int)blockIdx.x - rc.first_block) * blockDim.x + threadIdx.x);
+        return;
+    }
     const uint8_t* __restrict__ src = sa ? sa->x_u8 : src_arg;      // indirect step arguments
     const int chunks = ld / 16;
     const int64_t total = rows * chunks;
-    const int64_t gstride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t gstride = (int64_t)(rc.first_block ? rc.first_block : gridDim.x) * blockDim.x;
     const bool vec_ok = (cols % 16 == 0) && (((uintptr_t)src & 15) == 0);
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gstride) {
         const int64_t r = t / chunks;
@@ -251,19 +284,7 @@ f32_to_bf16_2d_kernel(const float* __restrict__ src, int ld_src, __nv_bfloat16* 
 __global__ void __launch_bounds__(256)
 recast_w2_kernel(const float* __restrict__ W2, __nv_bfloat16* __restrict__ w2c, int ldh,
                  __nv_bfloat16* __restrict__ w2t, int H, int C) {
-    const int h = blockIdx.x * blockDim.x + threadIdx.x;
-    if (h >= H) return;
-    float v[16];
-#pragma unroll
-    for (int c = 0; c < 16; ++c) v[c] = (c < C) ? W2[(size_t)c * H + h] : 0.f;
-#pragma unroll
-    for (int c = 0; c < 16; ++c)
-        if (c < C) w2c[(size_t)c * ldh + h] = __float2bfloat16_rn(v[c]);
-    if (w2t) {
-        uint4* d = reinterpret_cast<uint4*>(w2t + (size_t)h * 64);
-        d[0] = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
-        d[1] = make_uint4(pack2(v[8], v[9]), pack2(v[10], v[11]), pack2(v[12], v[13]), pack2(v[14], v[15]));
-    }
+    recast_w2_column(W2, w2c, ldh, w2t, H, C, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 }  // namespace
@@ -285,7 +306,22 @@ int cme_u8_to_bf16_rows_ind(const uint8_t* src, const CmeStepArgs* step_args, vo
     if (rows == 0) return 0;
     const int64_t total = rows * (ld / 16);
     u8_to_bf16_kernel<<<cme::stride_grid(total, 256, 8, 4), 256, 0, cme::as_stream(stream)>>>(
-        src, step_args, (__nv_bfloat16*)dst_bf16, rows, cols, ld, add_ones);
+        src, step_args, (__nv_bfloat16*)dst_bf16, rows, cols, ld, add_ones, RecastArgs{});
+    CME_LAUNCH_CHECK();
+    return 0;
+}
+
+int cme_mlp_stage_recast(const uint8_t* src, const CmeStepArgs* step_args, void* dst_bf16, int64_t rows, int cols,
+                         int ld, const float* W2, void* w2c, int ldh, void* w2t, int H, int C, void* stream) {
+    CME_CHECK_ARG((src || step_args) && dst_bf16 && rows > 0 && cols > 0, "cme_mlp_stage_recast: bad argument");
+    CME_CHECK_ARG(ld % 16 == 0 && ld >= cols + 1, "cme_mlp_stage_recast: ld (%d) must be a multiple of 16 and cover %d columns",
+                  ld, cols + 1);
+    CME_CHECK_ARG(((uintptr_t)dst_bf16 & 15) == 0, "cme_mlp_stage_recast: dst must be 16-byte aligned");
+    CME_CHECK_ARG(W2 && w2c && H > 0 && C >= 1 && C <= 16 && ldh >= H, "cme_mlp_stage_recast: bad W2 argument");
+    const int stage_blocks = cme::stride_grid(rows * (ld / 16), 256, 8, 4);
+    RecastArgs rc{W2, (__nv_bfloat16*)w2c, (__nv_bfloat16*)w2t, ldh, H, C, stage_blocks};
+    u8_to_bf16_kernel<<<stage_blocks + (H + 255) / 256, 256, 0, cme::as_stream(stream)>>>(
+        src, step_args, (__nv_bfloat16*)dst_bf16, rows, cols, ld, 1, rc);
     CME_LAUNCH_CHECK();
     return 0;
 }

@@ -104,7 +104,9 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
         CME_CUDA(cudaMemsetAsync(grads + g.o_w2, 0, sizeof(float) * (size_t)(g.n_total - g.o_w2), side_s));
         if (side_stream) CME_CUDA(cudaEventRecord(ev(1), side_s));
     }
-    if ((rc = cme_u8_to_bf16_rows_ind(x_u8, sa, p->xb, rows, g.D, g.ldx, 1, stream))) return rc;
+    // staging, and in the same launch the bf16 copies of the W2 the previous step's update left
+    if ((rc = cme_mlp_stage_recast(x_u8, sa, p->xb, rows, g.D, g.ldx, params + g.o_w2, p->w2c, g.ldh, p->w2t, g.H, g.C,
+                                   stream))) return rc;
     if (fused_fwd) {
         // forward pass in one kernel: the layer-2 logits ride on the A1 tiles while they are staged
         if (need_zero && side_stream) CME_CUDA(cudaStreamWaitEvent(main_s, ev(1), 0));
@@ -129,7 +131,7 @@ int cme_mlp_step_ex(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* lab
                                    p->pads_dev, p->nranks, p->unit_rows, p->pad_local + cme::kPadStatus, stream))) return rc;
         if ((rc = cme_mlp_update_stream_ind(p, lr, reg, sa != nullptr, stream))) return rc;
     }
-    return cme_mlp_recast_w2(params + g.o_w2, p->w2c, g.ldh, p->w2t, g.H, g.C, stream);
+    return 0;
 }
 
 int cme_mlp_step(const CmeMlpPlan* p, const uint8_t* x_u8, const int32_t* labels, int64_t rows, float lr,
@@ -187,8 +189,8 @@ int cme_mlp_plan_free_sync(CmeMlpPlan* p) {
 }
 
 int cme_mlp_step_launches(const CmeMlpPlan* p) {
-    // staging, forward GEMM, layer 2 (or its per-row tail), backward tail, dW1 (+ update), re-cast
-    return p ? (p->overlap ? 6 : 7) + (p->dw2_scratch ? 1 : 0) : 0;
+    // staging (+ re-cast of W2), forward GEMM, layer 2 (or its per-row tail), backward tail, dW1 (+ update)
+    return p ? (p->overlap ? 5 : 6) + (p->dw2_scratch ? 1 : 0) : 0;
 }
 
 }  // extern "C"

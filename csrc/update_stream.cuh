@@ -208,8 +208,9 @@ __device__ __forceinline__ void run_update(const UpdateArgs& a, int worker, int 
     bool aborted = false;
 
     // stream order put this kernel after the backward tail: my W2 / b2 gradients are complete
+    // (one rank: nobody on the other side of a link, no fence to pay for; the flag still counts)
     if (worker == 0 && tid < a.nranks) {
-        __threadfence_system();
+        if (a.nranks > 1) __threadfence_system();
         cme::red_relaxed_sys_add(a.pads[tid] + cme::kPadTail, 1u);
     }
     const int64_t first = ((int64_t)worker * nthreads + tid) * 4, step = (int64_t)nworkers * nthreads * 4;
@@ -254,11 +255,19 @@ __device__ __forceinline__ void run_update(const UpdateArgs& a, int worker, int 
     if (tid < 32) {
         uint32_t last = 0;
         if (tid == 0) {
-            __threadfence_system();
+            // one rank: the end of the kernel orders these stores for whatever runs next, and a
+            // system-scope fence costs microseconds (most of this kernel's time on a small model)
+            if (a.nranks > 1) __threadfence_system();
             last = atomicAdd(pad + cme::kPadDoneCtr, 1u) == (uint32_t)nworkers - 1 ? 1u : 0u;
         }
         last = __shfl_sync(0xffffffffu, last, 0);
-        if (last) {
+        if (last && a.nranks == 1) {
+            if (tid == 0) {
+                pad[cme::kPadDoneCtr] = 0;
+                pad[cme::kPadDone0] += 1u;
+                *reinterpret_cast<volatile uint32_t*>(pad + cme::kPadEpoch) = epoch;
+            }
+        } else if (last) {
             if (tid == 0) pad[cme::kPadDoneCtr] = 0;
             // every group fenced its stores at system scope before it counted itself out, and this
             // thread has seen all the counts: one more fence orders those observations before the bumps

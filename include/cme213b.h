@@ -404,6 +404,10 @@ int cme_mlp_update_stream(const CmeMlpPlan* plan, float lr, float reg, void* str
 int cme_mlp_update_stream_ind(const CmeMlpPlan* plan, float lr, float reg, int indirect, void* stream);
 int cme_u8_to_bf16_rows_ind(const uint8_t* src, const CmeStepArgs* step_args, void* dst_bf16, int64_t rows,
                             int cols, int ld, int add_ones, void* stream);
+/* The staging launch of a training step: uint8 rows -> bf16 rows with the ones column, and in
+ * extra blocks of the same launch the bf16 copies of W2 (cme_mlp_recast_w2). */
+int cme_mlp_stage_recast(const uint8_t* src, const CmeStepArgs* step_args, void* dst_bf16, int64_t rows, int cols,
+                         int ld, const float* W2, void* w2c, int ldh, void* w2t, int H, int C, void* stream);
 int cme_mlp_fwd2_tc_ind(const void* A1, const void* W2c, const float* b2, const int32_t* labels,
                         const CmeStepArgs* step_args, float* dz2, void* dz2b, float* loss_sum, int32_t* pred,
                         float* gb2, float scale, int64_t rows, int H, int ldh, int C, void* stream);
