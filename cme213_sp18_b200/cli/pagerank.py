@@ -26,7 +26,15 @@ def run_one(n, avg, iters, seed, check=True):
 
     ca, cb, out = (torch.empty_like(d[2]) for _ in range(3))
     # timed region = the kernels only, like the reference (ref hw2code/pagerank.cu:100-120)
-    ms = time_cuda_ms(lambda: dev.pagerank_iterate(d[0], d[1], d[2], d[3], ca, cb, out, iters), warmup=2, iters=5)
+    call = lambda: dev.pagerank_iterate(d[0], d[1], d[2], d[3], ca, cb, out, iters)   # noqa: E731
+    ms = time_cuda_ms(call, warmup=2, iters=5)
+    if ms < 0.2:
+        # a run this short is shorter than the interpreter's own cost of issuing it, and the GPU would
+        # be timed waiting for Python: time ten runs issued back to back and take the mean
+        def ten():
+            for _ in range(10):
+                call()
+        ms = time_cuda_ms(ten, warmup=1, iters=5) / 10
     ulp = host.max_ulp(out.cpu().numpy(), host.pagerank(rp, edges, r0, inv, iters))[0] if check else 0
     return ms, ulp
 

@@ -69,11 +69,11 @@ def pagerank_step(row_ptr, edges_ptr: int, contrib_in, inv_deg, rank_out, contri
 
 
 def pagerank_iterate(row_ptr, edges, rank0, inv_deg, contrib_a, contrib_b, rank_out, iterations: int) -> None:
-    """All iterations launched from native code (ref hw2code/pagerank.cu:59-136)."""
+    """All iterations in one cooperative launch with grid barriers (ref hw2code/pagerank.cu:59-136)."""
     check(device_lib().cme_pagerank_iterate(ptr(row_ptr), ptr(edges), ptr(rank0), ptr(inv_deg),
                                             ptr(contrib_a), ptr(contrib_b), ptr(rank_out), iterations,
                                             rank0.numel(), stream_ptr()), "cme_pagerank_iterate")
-    _count(iterations + 1)
+    _count(1)            # one cooperative launch: pre-scale + every iteration
 
 
 def pagerank_gen_edges(edges: torch.Tensor, edge_begin: int, num_nodes: int, seed: int) -> None:

@@ -12,6 +12,11 @@
 //    NVLink while other rows are still gathering).
 #include "common.cuh"
 
+#include <algorithm>
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
+
 namespace {
 
 __global__ void __launch_bounds__(256) prescale_kernel(const float* __restrict__ rank,
@@ -52,6 +57,57 @@ propagate_kernel(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict
             contrib_out[i] = c;
         } else {
             for (int p = 0; p < nranks; ++p) peer_contrib[p][i] = c;
+        }
+    }
+}
+
+// One row of the propagation: gathers in edge order, four in flight.  CG: contrib is read
+// through L2 only (the persistent kernel below re-reads a buffer another SM rewrote two
+// iterations earlier; an L1 line could be stale).
+template <bool CG>
+__device__ __forceinline__ float row_sum(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict__ edges,
+                                         const float* contrib_in, int64_t i) {
+    int64_t j = __ldg(row_ptr + i);
+    const int64_t end = __ldg(row_ptr + i + 1);
+    float sum = 0.f;
+    for (; j + 4 <= end; j += 4) {
+        const uint32_t e0 = __ldg(edges + j), e1 = __ldg(edges + j + 1), e2 = __ldg(edges + j + 2), e3 = __ldg(edges + j + 3);
+        const float c0 = CG ? __ldcg(contrib_in + e0) : __ldg(contrib_in + e0);
+        const float c1 = CG ? __ldcg(contrib_in + e1) : __ldg(contrib_in + e1);
+        const float c2 = CG ? __ldcg(contrib_in + e2) : __ldg(contrib_in + e2);
+        const float c3 = CG ? __ldcg(contrib_in + e3) : __ldg(contrib_in + e3);
+        sum += c0;
+        sum += c1;
+        sum += c2;
+        sum += c3;
+    }
+    for (; j < end; ++j) sum += CG ? __ldcg(contrib_in + __ldg(edges + j)) : __ldg(contrib_in + __ldg(edges + j));
+    return sum;
+}
+
+// All iterations in ONE cooperative launch: the pre-scale, then `iterations` propagation steps
+// separated by grid barriers.  The reference issues one launch per iteration
+// (ref hw2code/pagerank.cu:100-120); on its small graphs (32 k nodes, 64 k edges) an iteration is
+// ~2 us of work behind ~3 us of launch, which is where round 1 lost to it.  The rank vector is
+// written once, by the last iteration.
+__global__ void __launch_bounds__(256)
+iterate_persistent_kernel(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict__ edges,
+                          const float* __restrict__ rank0, const float* __restrict__ inv_deg,
+                          float* contrib_a, float* contrib_b, float* __restrict__ rank_out, int iterations,
+                          int64_t n, float base) {
+    cg::grid_group grid = cg::this_grid();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int64_t i = first; i < n; i += stride) contrib_a[i] = __ldg(rank0 + i) * __ldg(inv_deg + i);
+    for (int it = 0; it < iterations; ++it) {
+        grid.sync();
+        const float* in = (it & 1) ? contrib_b : contrib_a;
+        float* out = (it & 1) ? contrib_a : contrib_b;
+        const bool last = it + 1 == iterations;
+        for (int64_t i = first; i < n; i += stride) {
+            const float r = base + 0.5f * row_sum<true>(row_ptr, edges, in, i);
+            if (last) rank_out[i] = r;
+            else out[i] = r * __ldg(inv_deg + i);
         }
     }
 }
@@ -109,17 +165,24 @@ int cme_pagerank_iterate(const int64_t* row_ptr, const uint32_t* edges, const fl
     CME_CHECK_ARG(row_ptr && edges && rank0 && inv_deg && contrib_a && contrib_b && rank_out,
                   "cme_pagerank_iterate: null buffer");
     CME_CHECK_ARG(iterations >= 0 && num_nodes > 0, "cme_pagerank_iterate: bad argument");
-    int rc = cme_pagerank_prescale(rank0, inv_deg, contrib_a, num_nodes, stream);
-    if (rc) return rc;
-    float* bufs[2] = {contrib_a, contrib_b};
-    for (int it = 0; it < iterations; ++it) {
-        rc = cme_pagerank_step(row_ptr, edges, bufs[it & 1], inv_deg, rank_out, bufs[(it + 1) & 1],
-                               nullptr, 1, 0, num_nodes, num_nodes, stream);
-        if (rc) return rc;
-    }
-    if (iterations == 0)
+    if (iterations == 0) {
         CME_CUDA(cudaMemcpyAsync(rank_out, rank0, sizeof(float) * (size_t)num_nodes,
                                  cudaMemcpyDeviceToDevice, cme::as_stream(stream)));
+        return 0;
+    }
+    // every CTA must be resident for the grid barriers: size the grid from the occupancy of this device
+    static int per_sm = 0;
+    if (!per_sm) {
+        CME_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, iterate_persistent_kernel, 256, 0));
+        if (per_sm < 1) per_sm = 1;
+    }
+    const int64_t need = cme::ceil_div64(num_nodes, 256);
+    const int grid = (int)std::min<int64_t>(need, (int64_t)per_sm * cme::sm_count());
+    const float base = 0.5f / (float)num_nodes;
+    void* args[] = {(void*)&row_ptr, (void*)&edges, (void*)&rank0, (void*)&inv_deg, (void*)&contrib_a,
+                    (void*)&contrib_b, (void*)&rank_out, (void*)&iterations, (void*)&num_nodes, (void*)&base};
+    CME_CUDA(cudaLaunchCooperativeKernel((const void*)iterate_persistent_kernel, dim3(grid), dim3(256), args, 0,
+                                         cme::as_stream(stream)));
     return 0;
 }
 
