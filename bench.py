@@ -45,6 +45,8 @@ def parse():
                     help="sharded: every rank holds its slices in its own HBM; owner: rank 0 holds the "
                          "minibatches and every rank's staging kernel pulls its slice over NVLink "
                          "(the reference's MPI_Scatter, fused)")
+    ap.add_argument("--no-prefetch", action="store_true",
+                    help="owner mode: pull every slice inside its own step's staging kernel instead of one step ahead")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp64"],
                     help="fp64 = the grade-mode parity engine (the reference's precision)")
     ap.add_argument("--global-batch", type=int, default=0, help="override the config's global batch "
@@ -230,6 +232,9 @@ def run_ours(args) -> dict:
     def one_step(i):
         p = i % pool
         eng.step(x_ptrs[p], l_dev[p], in_proc, args.lr, args.reg, in_proc * world, graph=not args.no_graph)
+        if owner and not args.no_prefetch:
+            # the next minibatch's slice starts crossing NVLink now, under this step's kernels
+            eng.prefetch(x_ptrs[(i + 1) % pool], in_proc)
 
     one_step(0)                        # set-up: the first call records the step's graph
     sampler = ClockSampler(info.local_rank, period_ms=5).start() if rank == 0 else None
@@ -325,7 +330,8 @@ def run_ours(args) -> dict:
         "impl": "ours",
         "config": {"model": f"mlp-{H[0]}-{H[1]}-{H[2]}", "global_batch": gb, "seq_len": 1,
                    "parallelism": f"dp{world}", "comm": comm_name,
-                   "data_mode": "owner (rank 0 holds the minibatch, slices pulled over NVLink in the staging kernel)"
+                   "data_mode": ("owner (rank 0 holds the minibatch; every rank pulls its slice over NVLink "
+                                 + ("inside the staging kernel)" if args.no_prefetch else "one step ahead on a copy stream)"))
                    if owner else "sharded (every rank's slice resident in its own HBM)",
                    "l2": "per-step working set (activations) exceeds L2; inputs rotate over "
                          f"{pool} distinct minibatches" if args.config == "wide"

@@ -258,8 +258,10 @@ class MLPEngineBF16:
         minibatch position and every learning rate."""
         if rows > self.max_rows:
             raise ValueError(f"step: {rows} rows exceed the engine capacity {self.max_rows}")
+        x_u8_ptr, pf_slot = self._prefetched(x_u8_ptr, rows)
         if self.comm == "nccl" or self.tail != "tc":
             self._step_body(x_u8_ptr, labels, rows, lr, reg, norm, want_loss)
+            self._prefetch_consumed(pf_slot)
             return
         scale = 1.0 / norm
         if not graph:
@@ -267,6 +269,7 @@ class MLPEngineBF16:
                 self.loss.zero_()
             dev.mlp_step_native(self.plan, x_u8_ptr, labels, rows, lr, reg, scale,
                                 self.loss if want_loss else None, self.side_stream, self.ev)
+            self._prefetch_consumed(pf_slot)
             return
         dev.mlp_set_step_args(self.plan, x_u8_ptr, labels, lr, reg, scale)
         key = (rows, want_loss)
@@ -280,9 +283,58 @@ class MLPEngineBF16:
             n = dev.launches() - before
             dev._count(-n)
             self._graphs[key] = (g, n)
+            self._prefetch_consumed(pf_slot)
             return
         entry[0].replay()
         dev._count(entry[1])
+        self._prefetch_consumed(pf_slot)
+
+    # ---- owner-mode prefetch: the next step's slice crosses NVLink while this step computes ----
+    def prefetch(self, x_u8_ptr: int, rows: int) -> None:
+        """Start copying `rows` rows of uint8 pixels at the (peer-mapped) address x_u8_ptr into a
+        local buffer on a copy stream.  The next step() called with this address stages from the
+        local copy, so the pull over NVLink (the reference's MPI_Scatter of the minibatch,
+        ref fpcode/neural_network.cpp:460-481) is off the step's critical path.  Call it right
+        after issuing the step that precedes the one it feeds."""
+        if not hasattr(self, "_pf"):
+            d = self.info.device
+            n = self.max_rows * self.D + 48
+            self._pf = {"buf": [torch.empty(n, dtype=torch.uint8, device=d) for _ in range(2)],
+                        "ready": [torch.cuda.Event() for _ in range(2)],
+                        "read": [torch.cuda.Event() for _ in range(2)], "read_valid": [False, False],
+                        "src": [None, None], "next": 0,
+                        "stream": torch.cuda.Stream(device=d)}
+        pf = self._pf
+        slot = pf["next"]
+        pf["next"] ^= 1
+        nbytes = rows * self.D
+        first = x_u8_ptr - (x_u8_ptr % 16)              # whole 16-byte vectors covering the slice
+        span = (x_u8_ptr + nbytes - first + 15) // 16 * 16
+        cs = pf["stream"]
+        if pf["read_valid"][slot]:
+            cs.wait_event(pf["read"][slot])               # the step that staged from this slot is done
+        with torch.cuda.stream(cs):
+            dev.peer_copy(first, pf["buf"][slot], span)
+            pf["ready"][slot].record(cs)
+        pf["src"][slot] = (x_u8_ptr, rows, pf["buf"][slot].data_ptr() + x_u8_ptr % 16)
+
+    def _prefetched(self, x_u8_ptr: int, rows: int):
+        """(local address, slot) if this slice was prefetched, else (x_u8_ptr, None); makes the
+        current stream wait for the copy."""
+        pf = getattr(self, "_pf", None)
+        if pf is not None:
+            for slot in (0, 1):
+                src = pf["src"][slot]
+                if src is not None and src[0] == x_u8_ptr and src[1] >= rows:
+                    torch.cuda.current_stream().wait_event(pf["ready"][slot])
+                    pf["src"][slot] = None
+                    return src[2], slot
+        return x_u8_ptr, None
+
+    def _prefetch_consumed(self, slot) -> None:
+        if slot is not None:
+            self._pf["read"][slot].record()
+            self._pf["read_valid"][slot] = True
 
     def _indirect_step(self, rows: int, want_loss: bool) -> None:
         if want_loss:

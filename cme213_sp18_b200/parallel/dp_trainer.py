@@ -164,6 +164,13 @@ class DataParallelTrainer:
                     if self.precision == "bf16":
                         eng.step(self._data_base + lo * D, lab, in_proc, lr, reg, in_proc * world,
                                  want_loss=want_loss, graph=self.graph)
+                        if self.data_mode == "owner" and world > 1:
+                            # pull the next minibatch's slice from the owner while this step computes
+                            nb = batch + 1 if batch + 1 < num_batches else (0 if _epoch + 1 < epochs else None)
+                            if nb is not None:
+                                n_in = M.dp_in_proc(bs, N - nb * bs, world)
+                                if n_in > 0:
+                                    eng.prefetch(self._data_base + (nb * bs + info.rank * n_in) * D, n_in)
                     else:
                         src = self.data if not isinstance(self.data, SymmetricTensor) else None
                         if src is None:

@@ -1468,6 +1468,29 @@ int choose_ksplit(int tiles_mn, int kb_total, int sms) {
     return best;
 }
 
+// k-split of the CTA-pair dW1 kernel.  Measured on B200 (8192-wide model, dW1 alone / whole step):
+//   8192 rows   s = 1: 92 / 311 us    s = 4 (what filling every wave suggests): 98 / 341 us
+//   16384 rows  s = 1: 172 / 534      s = 4: 181 / 552
+//   65536 rows  s = 1: 656            s = 4: 651
+//   1024-wide model, 8192 rows (16 tiles for 74 pairs)   s = 1: 51 / 114    s = 4: 69 / 132
+// Two things the wave count does not see: the board is power-bound, so a ragged last wave costs
+// little (idle SMs lend their power to the busy ones), and the epilogue of a 256 x 256 fp32 tile
+// takes ~10 us, which a chunk shorter than ~40 k-blocks no longer hides, while the chunks of one
+// tile that run at the same time queue up behind each other (ordered split-K).  So: no split once
+// the tiles cover half the machine; below that the split that minimises
+// (kb / s) * 0.33 us + s * 13 us among those that keep every item resident.
+int choose_ksplit_pairs(int tiles, int kb_total, int npairs) {
+    if (2 * tiles >= npairs) return 1;
+    int bs = 1;
+    double bt = 1e30;
+    for (int s = 1; s <= 16 && (long long)tiles * s <= npairs; ++s) {
+        if (s > 1 && kb_total / s < 16) break;
+        const double t = 0.33 * ((kb_total + s - 1) / s) + 13.0 * s;
+        if (t < bt) { bt = t; bs = s; }
+    }
+    return bs;
+}
+
 // Small dW1 products (a handful of tiles): one SM pulls its operands out of L2 at ~100 GB/s, so a
 // k-block costs about c = 0.10 + 0.0018 * BN microseconds and every chained epilogue of the ordered
 // split-K about e = 0.9 + 0.009 * BN (fitted on the 784-100-10 model, 3200 rows: 34 us with one
@@ -1640,13 +1663,13 @@ static int dw1_launch(const void* dZ1, const void* X, float* gW1, int64_t rows, 
         const int m2 = (H + 255) / 256, n2 = (K + 255) / 256;
         const int BN2 = 256;
         const int npairs = cme::sm_count() / 2;
-        const int ks = choose_ksplit(m2 * n2, kb_total, npairs);
+        const int ks = dev_ks > 0 ? std::min(dev_ks, std::max(1, kb_total / 8)) : choose_ksplit_pairs(m2 * n2, kb_total, npairs);
         CME_CHECK_ARG(m2 * n2 * 2 <= kDwPartWords && m2 <= kDwUnitWords && m2 <= cme::kPadMaxUnits,
                       "cme_mlp_dw1: %d x %d tiles exceed the counter scratch", m2, n2);
         sy.parts_per_tile = n2 * 2;
         sy.tiles_per_unit = 1;
         sy.m_tiles = m2;
-        sy.sblocks = (kb_total / ks >= 128) ? std::min(m2, 4) : 1;
+        sy.sblocks = (ks > 1 && kb_total / ks >= 128) ? std::min(m2, 4) : 1;
         if ((rc = opt_in_smem(gemm_mnmajor2_kernel, kSmemMNMajor2))) return rc;
         const long long items2 = (long long)m2 * n2 * ks;
         const int pairs = (int)std::min<long long>(items2, npairs);
