@@ -133,11 +133,16 @@ def self_check(args, H, gb, info, trainer_comm) -> dict:
     eng = MLPEngineBF16(H, in_proc, info, comm=trainer_comm)
     l1 = run(eng, xs, ls, in_proc, gb // world * world, graph=not args.no_graph)
     d1 = digest(eng)
+    tail1 = eng.params.tensor[eng.o_w2:].clone()
     snap = M.NeuralNetwork(H)
     eng.store_params(snap)
     run(eng, xs, ls, in_proc, gb // world * world, graph=not args.no_graph)
     d2 = digest(eng)
     reproducible = bool(torch.equal(d1, d2))
+    # the one-kernel forward + slot-wise dW2 path stores every gradient in a fixed order; narrow
+    # models (hidden width not a multiple of 256) still add dW2 / db2 with atomics
+    deterministic_path = eng.fwd_scratch is not None and eng.dw2_scratch is not None
+    rerun_diff = float((eng.params.tensor[eng.o_w2:] - tail1).abs().max() / tail1.abs().max())
     if world > 1:
         all_d = [torch.zeros_like(d1) for _ in range(world)]
         dist.all_gather(all_d, d1)
@@ -150,7 +155,8 @@ def self_check(args, H, gb, info, trainer_comm) -> dict:
     del eng
     out = {"steps": steps, "lr": lr, "loss_first": l1[0] / gb, "loss_last": l1[-1] / gb,
            "loss_falls": l1[-1] < l1[0] - 0.02 * gb, "replicas_bit_identical": identical,
-           "rerun_bit_identical": reproducible}
+           "rerun_bit_identical": reproducible, "rerun_max_rel_diff_w2": rerun_diff,
+           "fixed_order_path": deterministic_path}
     # one-rank oracle on rank 0: same global batch, eager, single stream
     if rank == 0:
         torch.cuda.empty_cache()
@@ -172,7 +178,10 @@ def self_check(args, H, gb, info, trainer_comm) -> dict:
         del solo
         torch.cuda.empty_cache()
     barrier(info)
-    out["ok"] = bool(out["loss_falls"] and identical and reproducible and out.get("matches_one_rank", True))
+    # bit-identical reruns are required where every sum has a fixed order; elsewhere the two runs
+    # may differ by the rounding of the atomics' arrival order and no more
+    rerun_ok = reproducible if deterministic_path else rerun_diff < 1e-5
+    out["ok"] = bool(out["loss_falls"] and identical and rerun_ok and out.get("matches_one_rank", True))
     return out
 
 

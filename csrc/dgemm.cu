@@ -101,6 +101,19 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 
 constexpr int MK = 16;   // k-block of the shared-memory kernel
 
+__device__ __forceinline__ double ld_dsmem_f64(const double* local, uint32_t cta) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(local);
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(cta));
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(ra) : "memory");
+    return v;
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+
 // 8 warps as 4 (M) x 2 (N); a warp owns (BM/4) x (BN/2) of the block tile as m8n8 fragments.
 // Shared layouts keep the dimension that is contiguous in global memory contiguous in shared
 // memory (conflict-free stores), with row strides chosen so that a fragment read (8 values of g,
@@ -109,13 +122,21 @@ constexpr int MK = 16;   // k-block of the shared-memory kernel
 template <int BM_, int BN_, bool TA, bool TB>
 __global__ void __launch_bounds__(256, (BM_ == 64 ? 2 : 1))
 dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A, int lda,
-                 const double* __restrict__ B, int ldb, double beta, double* __restrict__ C, int ldc) {
+                 const double* __restrict__ B, int ldb, double beta, double* __restrict__ C, int ldc,
+                 int k_per_cta) {
     constexpr int SA = TA ? MK + 4 : BM_ + 8;
     constexpr int SB = TB ? BN_ + 8 : MK + 4;
     constexpr int AE = BM_ * MK / 256, BE = BN_ * MK / 256;
     constexpr int WM = BM_ / 4, WN = BN_ / 2, MT = WM / 8, NT = WN / 8;
-    __shared__ double As[TA ? BM_ * SA : MK * SA];
-    __shared__ double Bs[TB ? MK * SB : BN_ * SB];
+    constexpr int kAsz = TA ? BM_ * SA : MK * SA, kBsz = TB ? MK * SB : BN_ * SB;
+    // split-K over a cluster (gridDim.z CTAs, 64 x 64 tiles only): the operand buffers are reused
+    // for the partial tile, [n][m] with rows of BM_ + 2 doubles
+    constexpr int RS = BM_ + 2;
+    constexpr int kRed = BM_ == 64 ? BN_ * RS : 0;
+    __shared__ double smem_all[(kAsz + kBsz > kRed) ? kAsz + kBsz : kRed];
+    double* As = smem_all;
+    double* Bs = smem_all + kAsz;
+    const int k_begin = (int)blockIdx.z * k_per_cta, k_end = min(K, k_begin + k_per_cta);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int m0 = blockIdx.x * BM_, n0 = blockIdx.y * BN_;
     const int wm0 = (warp & 3) * WM, wn0 = (warp >> 2) * WN;
@@ -132,19 +153,19 @@ dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A
             const int e = tid + x * 256;
             const int m = TA ? e / MK : e % BM_, k = TA ? e % MK : e / BM_;
             const int gm = m0 + m, gk = k0 + k;
-            ra[x] = (gm < M && gk < K) ? (TA ? A[(size_t)gk + (size_t)lda * gm] : A[(size_t)gm + (size_t)lda * gk]) : 0.0;
+            ra[x] = (gm < M && gk < k_end) ? (TA ? A[(size_t)gk + (size_t)lda * gm] : A[(size_t)gm + (size_t)lda * gk]) : 0.0;
         }
 #pragma unroll
         for (int x = 0; x < BE; ++x) {
             const int e = tid + x * 256;
             const int n = TB ? e % BN_ : e / MK, k = TB ? e / BN_ : e % MK;
             const int gn = n0 + n, gk = k0 + k;
-            rb[x] = (gn < N && gk < K) ? (TB ? B[(size_t)gn + (size_t)ldb * gk] : B[(size_t)gk + (size_t)ldb * gn]) : 0.0;
+            rb[x] = (gn < N && gk < k_end) ? (TB ? B[(size_t)gn + (size_t)ldb * gk] : B[(size_t)gk + (size_t)ldb * gn]) : 0.0;
         }
     };
 
-    gload(0);
-    for (int k0 = 0; k0 < K; k0 += MK) {
+    gload(k_begin);
+    for (int k0 = k_begin; k0 < k_end; k0 += MK) {
 #pragma unroll
         for (int x = 0; x < AE; ++x) {
             const int e = tid + x * 256;
@@ -158,7 +179,7 @@ dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A
             Bs[TB ? k * SB + n : n * SB + k] = rb[x];
         }
         __syncthreads();
-        if (k0 + MK < K) gload(k0 + MK);       // in flight while the tensor pipe works on this block
+        if (k0 + MK < k_end) gload(k0 + MK);       // in flight while the tensor pipe works on this block
 #pragma unroll
         for (int kk = 0; kk < MK; kk += 4) {
             double a[MT], b[NT];
@@ -179,6 +200,33 @@ dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A
                 for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
         __syncthreads();
+    }
+    if (BM_ == 64 && gridDim.z > 1) {
+        // every CTA of the cluster leaves its partial tile in shared memory; CTA r then adds rows
+        // [r * BM_/S, (r+1) * BM_/S) of all of them in CTA order and writes that part of C
+        const int S = gridDim.z, r = blockIdx.z;
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int x = 0; x < 2; ++x)
+#pragma unroll
+                for (int i = 0; i < MT; ++i)
+                    smem_all[(wn0 + j * 8 + 2 * t + x) * RS + wm0 + i * 8 + g] = acc[i][j][x];
+        cluster_barrier();
+        const int rows_per = BM_ / S;                 // S is 2, 4 or 8
+        for (int e = tid; e < rows_per * BN_; e += 256) {
+            const int m = r * rows_per + e % rows_per, n = e / rows_per;
+            const double* cell = &smem_all[n * RS + m];
+            double v = ld_dsmem_f64(cell, 0);
+            for (int c = 1; c < S; ++c) v += ld_dsmem_f64(cell, (uint32_t)c);
+            const int gm = m0 + m, gn = n0 + n;
+            if (gm < M && gn < N) {
+                double* cp = C + (size_t)gm + (size_t)ldc * gn;
+                *cp = (beta == 0.0) ? alpha * v : alpha * v + beta * (*cp);
+            }
+        }
+        cluster_barrier();                            // nobody leaves while its tile is being read
+        return;
     }
 #pragma unroll
     for (int j = 0; j < NT; ++j)
@@ -205,18 +253,6 @@ dgemm_mma_kernel(int M, int N, int K, double alpha, const double* __restrict__ A
 // come straight from global memory: every operand element is used once per cluster, and a
 // fragment load is eight 32-byte sectors, all of them used, whichever dimension is contiguous.
 constexpr int SK_I = 64, SK_J = 16, SK_LD = SK_I + 4;      // partial tile [j][i], rows of 68 doubles
-
-__device__ __forceinline__ double ld_dsmem_f64(const double* local, uint32_t cta) {
-    const uint32_t a = (uint32_t)__cvta_generic_to_shared(local);
-    uint32_t ra;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(cta));
-    double v;
-    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(ra) : "memory");
-    return v;
-}
-__device__ __forceinline__ void cluster_barrier() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
 
 __global__ void __launch_bounds__(256)
 dgemm_skinny_kernel(int I, int J, int K, double alpha, const double* __restrict__ A, int64_t ai, int64_t ak,
@@ -403,17 +439,36 @@ int dgemm_check(int transA, int transB, int M, int N, int K, const double* A, in
     return 0;
 }
 
-template <int BM_, int BN_>
-int launch_mma(bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B,
-               int ldb, double beta, double* C, int ldc, cudaStream_t st) {
-    dim3 grid((M + BM_ - 1) / BM_, (N + BN_ - 1) / BN_);
-    CME_CHECK_ARG(grid.y < 65536, "cme_dgemm: N too large for one launch");
-    if (!ta && !tb) dgemm_mma_kernel<BM_, BN_, false, false><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
-    else if (ta && !tb) dgemm_mma_kernel<BM_, BN_, true, false><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
-    else if (!ta && tb) dgemm_mma_kernel<BM_, BN_, false, true><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
-    else dgemm_mma_kernel<BM_, BN_, true, true><<<grid, 256, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
-    CME_LAUNCH_CHECK();
+template <int BM_, int BN_, bool TA, bool TB>
+int launch_mma_t(dim3 grid, int S, int k_per, int M, int N, int K, double alpha, const double* A, int lda,
+                 const double* B, int ldb, double beta, double* C, int ldc, cudaStream_t st) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(256, 1, 1);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = S;
+    cfg.attrs = attr;
+    cfg.numAttrs = S > 1 ? 1 : 0;
+    CME_CUDA(cudaLaunchKernelEx(&cfg, dgemm_mma_kernel<BM_, BN_, TA, TB>, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc,
+                                k_per));
     return 0;
+}
+
+// S > 1 (64 x 64 tiles only): K is split over a cluster of S CTAs, see the kernel's epilogue
+template <int BM_, int BN_>
+int launch_mma(bool ta, bool tb, int S, int M, int N, int K, double alpha, const double* A, int lda, const double* B,
+               int ldb, double beta, double* C, int ldc, cudaStream_t st) {
+    dim3 grid((M + BM_ - 1) / BM_, (N + BN_ - 1) / BN_, S);
+    CME_CHECK_ARG(grid.y < 65536, "cme_dgemm: N too large for one launch");
+    const int k_per = S > 1 ? ((K + S - 1) / S + MK - 1) / MK * MK : (K > 0 ? K : 1);
+    if (!ta && !tb) return launch_mma_t<BM_, BN_, false, false>(grid, S, k_per, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    if (ta && !tb) return launch_mma_t<BM_, BN_, true, false>(grid, S, k_per, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    if (!ta && tb) return launch_mma_t<BM_, BN_, false, true>(grid, S, k_per, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    return launch_mma_t<BM_, BN_, true, true>(grid, S, k_per, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
 }
 
 int launch_skinny(bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B,
@@ -462,8 +517,14 @@ int cme_dgemm(int transA, int transB, int M, int N, int K, double alpha, const d
     // 128x128 tiles once they fill the machine; below that 64x64 tiles, two CTAs per SM
     const int64_t big_tiles = (int64_t)((M + 127) / 128) * ((N + 127) / 128);
     if (big_tiles >= cme::sm_count())
-        return launch_mma<128, 128>(ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
-    return launch_mma<64, 64>(ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+        return launch_mma<128, 128>(ta, tb, 1, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
+    // 64 x 64 tiles, two CTAs per SM.  Too few of them leave SMs idle or unevenly loaded (ncu on
+    // (1000,800,784): DMMA pipe 67 % busy on the SMs that got two tiles, 33 % on those with one),
+    // so K is split over a cluster until the CTAs cover the machine twice, at least 64 deep each.
+    const int64_t tiles = (int64_t)((M + 63) / 64) * ((N + 63) / 64);
+    int S = 1;
+    while (S < 8 && tiles * S < 2 * cme::sm_count() && K / (2 * S) >= 64) S *= 2;
+    return launch_mma<64, 64>(ta, tb, S, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, st);
 }
 
 /* The round-1 CUDA-core kernel (64x64 tiles, 4x4 outputs per thread), for A/B timing only. */

@@ -25,6 +25,7 @@
 #include "tc_host.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -508,6 +509,8 @@ int cme_mlp_fwd_fused(const void* X, const void* W1c, const void* W2c, const flo
     const int m_blocks = (int)((rows + 255) / 256), n2 = Hp / 256;
     const int npairs = cme::sm_count() / 2;
     int slices = choose_slices(m_blocks, n2, npairs);
+    static const int dev_slices = getenv("CME_FWD_SLICES") ? atoi(getenv("CME_FWD_SLICES")) : 0;      // tuning hook
+    if (dev_slices > 0 && n2 % dev_slices == 0) slices = dev_slices;
     const int64_t part_floats = std::max<int64_t>(4 * max_rows, 32 * std::min<int64_t>(max_rows, 16384)) * 16;
     while (slices > 1 && (int64_t)slices * max_rows * 16 > part_floats) slices /= 2;
     CUtensorMap tmA, tmB, tmC, tmW;

@@ -34,6 +34,8 @@ G = torch.zeros((eng.Hp, eng.ldx), device="cuda")
 res = {}
 res["dw1_plain"] = timed(lambda: dev.mlp_dw1(eng.dz1, eng.xb, G, rows, eng.K, eng.Hh, eng.ldx))
 res["fwd1"] = timed(lambda: dev.mlp_fwd1(eng.xb, eng.w1c.tensor, eng.a1, rows, eng.K, eng.Hh))
+if eng.fwd_scratch is not None:
+    res["fwd_fused+tail"] = timed(lambda: dev.mlp_fwd_fused(eng.xb, eng.w1c.tensor, eng.w2c, eng.params.tensor[eng.o_b2:], lab, eng.a1, eng.dz2, eng.dz2b, eng.loss, eng.pred, eng.grads.tensor[eng.o_b2:], eng.fwd_scratch, eng.max_rows, 1.0 / rows, rows, eng.K, eng.Hh, eng.C))
 res["stage"] = timed(lambda: eng.stage(x.data_ptr(), rows))
 res["step_graph"] = timed(lambda: eng.step(x.data_ptr(), lab, rows, 0.01, 1e-4, rows, graph=False), reps=10)
 print(json.dumps({k: round(v, 2) for k, v in res.items()}))
