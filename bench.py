@@ -243,7 +243,7 @@ def run_ours(args) -> dict:
         eng.step(x_ptrs[p], l_dev[p], in_proc, args.lr, args.reg, in_proc * world, graph=not args.no_graph)
         if owner and not args.no_prefetch:
             # the next minibatch's slice starts crossing NVLink now, under this step's kernels
-            eng.prefetch(x_ptrs[(i + 1) % pool], in_proc)
+            eng.prefetch(x_ptrs[(i + 1) % pool], in_proc, local=rank == 0)
 
     one_step(0)                        # set-up: the first call records the step's graph
     sampler = ClockSampler(info.local_rank, period_ms=5).start() if rank == 0 else None

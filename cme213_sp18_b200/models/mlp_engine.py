@@ -290,12 +290,15 @@ class MLPEngineBF16:
         self._prefetch_consumed(pf_slot)
 
     # ---- owner-mode prefetch: the next step's slice crosses NVLink while this step computes ----
-    def prefetch(self, x_u8_ptr: int, rows: int) -> None:
+    def prefetch(self, x_u8_ptr: int, rows: int, local: bool = False) -> None:
         """Start copying `rows` rows of uint8 pixels at the (peer-mapped) address x_u8_ptr into a
         local buffer on a copy stream.  The next step() called with this address stages from the
         local copy, so the pull over NVLink (the reference's MPI_Scatter of the minibatch,
         ref fpcode/neural_network.cpp:460-481) is off the step's critical path.  Call it right
-        after issuing the step that precedes the one it feeds."""
+        after issuing the step that precedes the one it feeds.  local=True (the address is in this
+        GPU's own memory: the owner rank itself) does nothing: a copy would only cost bandwidth."""
+        if local:
+            return
         if not hasattr(self, "_pf"):
             d = self.info.device
             n = self.max_rows * self.D + 48

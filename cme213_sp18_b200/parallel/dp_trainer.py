@@ -170,7 +170,8 @@ class DataParallelTrainer:
                             if nb is not None:
                                 n_in = M.dp_in_proc(bs, N - nb * bs, world)
                                 if n_in > 0:
-                                    eng.prefetch(self._data_base + (nb * bs + info.rank * n_in) * D, n_in)
+                                    eng.prefetch(self._data_base + (nb * bs + info.rank * n_in) * D, n_in,
+                                                 local=info.rank == 0)
                     else:
                         src = self.data if not isinstance(self.data, SymmetricTensor) else None
                         if src is None:
