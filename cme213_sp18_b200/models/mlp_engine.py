@@ -317,7 +317,7 @@ class MLPEngineBF16:
         if pf["read_valid"][slot]:
             cs.wait_event(pf["read"][slot])               # the step that staged from this slot is done
         with torch.cuda.stream(cs):
-            dev.peer_copy(first, pf["buf"][slot], span)
+            dev.peer_copy(first, pf["buf"][slot], span, max_blocks=64)
             pf["ready"][slot].record(cs)
         pf["src"][slot] = (x_u8_ptr, rows, pf["buf"][slot].data_ptr() + x_u8_ptr % 16)
 

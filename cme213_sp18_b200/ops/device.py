@@ -416,8 +416,9 @@ def peer_barrier(pads_dev: torch.Tensor, rank: int, nranks: int, channel: int, e
     _count()
 
 
-def peer_copy(src_ptr: int, dst: torch.Tensor, nbytes: int) -> None:
-    check(device_lib().cme_peer_copy(src_ptr, ptr(dst), nbytes, stream_ptr()), "cme_peer_copy")
+def peer_copy(src_ptr: int, dst: torch.Tensor, nbytes: int, max_blocks: int = 0) -> None:
+    """Copy from a (peer-mapped) address with this repo's copy kernel; max_blocks caps its grid."""
+    check(device_lib().cme_peer_copy_bg(src_ptr, ptr(dst), nbytes, max_blocks, stream_ptr()), "cme_peer_copy")
     _count()
 
 

@@ -441,11 +441,18 @@ int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, u
 }
 
 int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream) {
+    return cme_peer_copy_bg(src, dst, bytes, 0, stream);
+}
+
+/* max_blocks > 0 caps the grid: a copy that runs next to compute kernels (the owner-mode prefetch)
+ * is bound by NVLink, not by SMs; 64 blocks keep ~1 MB in flight and leave the SMs to the GEMMs. */
+int cme_peer_copy_bg(const void* src, void* dst, size_t bytes, int max_blocks, void* stream) {
     CME_CHECK_ARG(src && dst && bytes % 16 == 0, "cme_peer_copy: 16-byte multiples only");
     if (bytes == 0) return 0;
     const size_t n16 = bytes / 16;
-    peer_copy_kernel<<<cme::stride_grid((int64_t)n16, 256, 8, 2), 256, 0, cme::as_stream(stream)>>>(
-        (const uint4*)src, (uint4*)dst, n16);
+    int grid = cme::stride_grid((int64_t)n16, 256, 8, 2);
+    if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
+    peer_copy_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>((const uint4*)src, (uint4*)dst, n16);
     CME_LAUNCH_CHECK();
     return 0;
 }

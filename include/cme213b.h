@@ -470,6 +470,8 @@ int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, u
                      int do_signal, int do_wait, void* stream);
 /* P2P copy bandwidth probe: dst (local) <- src (peer), 128-bit loads. */
 int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream);
+/* The same copy with the grid capped at max_blocks (0 = no cap), for copies that run beside compute. */
+int cme_peer_copy_bg(const void* src, void* dst, size_t bytes, int max_blocks, void* stream);
 
 #ifdef __cplusplus
 }
