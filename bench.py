@@ -109,7 +109,7 @@ def self_check(args, H, gb, info, trainer_comm) -> dict:
     world, rank = info.world, info.rank
     in_proc = gb // world
     # a step size at which plain SGD from the reference's 0.01 * randn start descends at this width
-    steps, lr = 10, (0.005 if H[1] >= 1024 else 0.2)
+    steps, lr = 10, (0.005 if H[1] >= 4096 else 0.05 if H[1] >= 512 else 0.2)
     x, lab = mnist.synthetic_mnist(gb, seed=77, pixel_max=1)
     nn0 = M.NeuralNetwork(H)
     xs = x[rank * in_proc:(rank + 1) * in_proc].to(info.device)
