@@ -448,7 +448,7 @@ def run_ours_fp64(args, info) -> dict:
     if not args.no_check:
         # N ranks against ONE rank on the same global batch, both in fp64: the reference's own
         # criterion (max-norm relative error below 1e-7, ref fpcode/utils/tests.cpp:51-75)
-        steps, lr = 10, (0.05 if H[1] >= 1000 else 0.2)
+        steps, lr = 10, (0.005 if H[1] >= 4096 else 0.05 if H[1] >= 512 else 0.2)
         x, lab = mnist.synthetic_mnist(gb, seed=77, pixel_max=1)
         nn0 = M.NeuralNetwork(H)
         xr = x[rank * in_proc:(rank + 1) * in_proc].to(info.device)

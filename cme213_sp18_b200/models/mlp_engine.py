@@ -311,15 +311,16 @@ class MLPEngineBF16:
         slot = pf["next"]
         pf["next"] ^= 1
         nbytes = rows * self.D
-        first = x_u8_ptr - (x_u8_ptr % 16)              # whole 16-byte vectors covering the slice
-        span = (x_u8_ptr + nbytes - first + 15) // 16 * 16
         cs = pf["stream"]
         if pf["read_valid"][slot]:
             cs.wait_event(pf["read"][slot])               # the step that staged from this slot is done
         with torch.cuda.stream(cs):
-            dev.peer_copy(first, pf["buf"][slot], span, max_blocks=64)
+            # on a copy engine: the step's persistent GEMM kernels hold every SM's registers, and a
+            # copy KERNEL was only scheduled in the gaps between them (8 GPUs: 0.374 ms/step against
+            # 0.382 without any prefetch and 0.330 with the data already local)
+            dev.peer_memcpy(x_u8_ptr, pf["buf"][slot], nbytes)
             pf["ready"][slot].record(cs)
-        pf["src"][slot] = (x_u8_ptr, rows, pf["buf"][slot].data_ptr() + x_u8_ptr % 16)
+        pf["src"][slot] = (x_u8_ptr, rows, pf["buf"][slot].data_ptr())
 
     def _prefetched(self, x_u8_ptr: int, rows: int):
         """(local address, slot) if this slice was prefetched, else (x_u8_ptr, None); makes the

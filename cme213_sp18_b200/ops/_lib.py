@@ -86,6 +86,7 @@ _DEV_SIGS = {
     "cme_peer_barrier": [P, c_int, c_int, c_int, c_u32, c_int, c_int, P],
     "cme_peer_copy": [P, P, c_size_t, P],
     "cme_peer_copy_bg": [P, P, c_size_t, c_int, P],
+    "cme_peer_memcpy": [P, P, c_size_t, P],
 }
 _DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes": c_size_t,
                  "cme_mlp_fwd_scratch_floats": c_size_t, "cme_mlp_bwd_tail_scratch_floats": c_size_t}

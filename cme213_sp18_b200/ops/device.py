@@ -409,6 +409,11 @@ def allreduce_sgd_f64(grad_ptrs, param_ptrs, pads_dev: torch.Tensor, rank: int, 
     _count()
 
 
+def peer_memcpy(src_ptr: int, dst: torch.Tensor, nbytes: int) -> None:
+    """Copy from a (peer-mapped) address on a copy engine (no SMs involved)."""
+    check(device_lib().cme_peer_memcpy(src_ptr, ptr(dst), nbytes, stream_ptr()), "cme_peer_memcpy")
+
+
 def peer_barrier(pads_dev: torch.Tensor, rank: int, nranks: int, channel: int, epoch: int,
                  signal: bool = True, wait: bool = True) -> None:
     check(device_lib().cme_peer_barrier(ptr(pads_dev), rank, nranks, channel, epoch & 0xFFFFFFFF,

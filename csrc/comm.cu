@@ -444,6 +444,16 @@ int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream) {
     return cme_peer_copy_bg(src, dst, bytes, 0, stream);
 }
 
+/* The same transfer on a copy engine instead of SMs (plain cudaMemcpyAsync, device to device through
+ * the peer mapping): for copies that must make progress WHILE persistent GEMM kernels hold every
+ * SM's registers (the owner-mode prefetch: a copy kernel only got scheduled between those kernels). */
+int cme_peer_memcpy(const void* src, void* dst, size_t bytes, void* stream) {
+    CME_CHECK_ARG(src && dst, "cme_peer_memcpy: null pointer");
+    if (bytes == 0) return 0;
+    CME_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, cme::as_stream(stream)));
+    return 0;
+}
+
 /* max_blocks > 0 caps the grid: a copy that runs next to compute kernels (the owner-mode prefetch)
  * is bound by NVLink, not by SMs; 64 blocks keep ~1 MB in flight and leave the SMs to the GEMMs. */
 int cme_peer_copy_bg(const void* src, void* dst, size_t bytes, int max_blocks, void* stream) {

@@ -472,6 +472,9 @@ int cme_peer_barrier(uint32_t* const* pads, int rank, int nranks, int channel, u
 int cme_peer_copy(const void* src, void* dst, size_t bytes, void* stream);
 /* The same copy with the grid capped at max_blocks (0 = no cap), for copies that run beside compute. */
 int cme_peer_copy_bg(const void* src, void* dst, size_t bytes, int max_blocks, void* stream);
+/* The same transfer on a copy engine (cudaMemcpyAsync through the peer mapping): makes progress
+ * while persistent kernels occupy every SM. */
+int cme_peer_memcpy(const void* src, void* dst, size_t bytes, void* stream);
 
 #ifdef __cplusplus
 }
