@@ -46,8 +46,17 @@ def main(argv=None) -> int:
     ap.add_argument("--iters", type=int, default=6)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-check", action="store_true")
+    ap.add_argument("--l2-fetch", type=int, default=0, choices=[0, 32, 64, 128],
+                    help="L2 fetch granularity in bytes for the run (0 = leave the driver's default of 64); "
+                         "measured: 32 changes nothing at 64 M nodes (51.79 vs 51.83 ms), HBM fetches 64 bytes anyway")
     args = ap.parse_args(argv)
     info = init_distributed()
+    if args.l2_fetch and torch.cuda.is_available():
+        from ..ops import device as dev
+
+        was = dev.l2_fetch_granularity(args.l2_fetch)
+        if info.is_main:
+            print(f"L2 fetch granularity {was} -> {args.l2_fetch} bytes")
     ok = True
     if info.world > 1 or args.nodes is not None:
         from ..parallel.pagerank_multi import PageRankShards

@@ -25,6 +25,7 @@ P = c_void_p  # every device pointer travels as void*
 _DEV_SIGS = {
     "cme_version": [],
     "cme_device_info": [P, P, P],
+    "cme_l2_fetch_granularity": [c_int, P],
     "cme_shift_bytes": [P, P, c_size_t, c_u8, c_int, P],
     "cme_pagerank_prescale": [P, P, P, c_i64, P],
     "cme_pagerank_step": [P, P, P, P, P, P, P, c_int, c_i64, c_i64, c_i64, P],

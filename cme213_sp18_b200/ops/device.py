@@ -32,6 +32,16 @@ def device_info():
     return {"sm_count": sm.value, "cc": (maj.value, mnr.value)}
 
 
+def l2_fetch_granularity(nbytes: int = 0) -> int:
+    """Set the device's L2 fetch granularity (32 / 64 / 128 bytes; 0 = only query); returns the
+    previous value.  Gather-heavy kernels (PageRank on graphs larger than L2) gain from 32."""
+    import ctypes as C
+
+    old = C.c_int(0)
+    check(device_lib().cme_l2_fetch_granularity(nbytes, C.addressof(old)), "cme_l2_fetch_granularity")
+    return old.value
+
+
 # ------------------------------------------------------------------ hw2 q1
 SHIFT_VARIANTS = {"char": 0, "uint": 1, "uint2": 2, "uint4": 3}
 

@@ -24,6 +24,9 @@ const char* cme_last_error(void);
 int cme_version(void);
 /* sm_count / cc_major / cc_minor of the current device (any may be NULL). */
 int cme_device_info(int* sm_count, int* cc_major, int* cc_minor);
+/* Get (and, if bytes > 0, set) the L2 fetch granularity of the current device: 32, 64 or 128 bytes.
+ * Device-wide hint; the previous value comes back in *old_bytes. */
+int cme_l2_fetch_granularity(int bytes, int* old_bytes);
 /* Creates the context, loads the module and runs one trivial kernel, then waits for it
  * (the reference's device_add_one warm-up, ref fpcode/gpu_func.cu:11-36). *value_inout += 1. */
 int cme_warmup(int* value_inout);
