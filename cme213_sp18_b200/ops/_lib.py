@@ -31,6 +31,7 @@ _DEV_SIGS = {
     "cme_pagerank_step": [P, P, P, P, P, P, P, c_int, c_i64, c_i64, c_i64, P],
     "cme_pagerank_iterate": [P, P, P, P, P, P, P, c_int, c_i64, P],
     "cme_pagerank_gen_edges": [P, c_i64, c_i64, c_i64, c_u64, P],
+    "cme_pagerank_block_step": [P, P, P, P, P, P, P, P, c_int, c_i64, c_i64, c_i64, c_int, c_int, P],
     "cme_heat_step": [P, P, c_int, c_int, c_int, c_float, c_float, c_int, c_int, c_float, P],
     "cme_heat_bc": [P, P, c_int, c_int, c_int, c_float, P],
     "cme_heat_slab_step": [P, P, P, P, c_int, c_int, c_int, c_float, c_float, c_float, c_int, c_int, P],

@@ -86,6 +86,18 @@ def pagerank_iterate(row_ptr, edges, rank0, inv_deg, contrib_a, contrib_b, rank_
     _count(1)            # one cooperative launch: pre-scale + every iteration
 
 
+def pagerank_block_step(blk_ptr_addr: int, edges_b, contrib_in, partial, inv_deg, rank_out, contrib_out,
+                        row_begin: int, nrows: int, num_nodes: int, first: bool, last: bool,
+                        peer_contrib: torch.Tensor | None = None, nranks: int = 1) -> None:
+    """One pass of the column-blocked propagation; blk_ptr_addr is the address of this block's
+    nrows + 1 int32 offsets into edges_b."""
+    check(device_lib().cme_pagerank_block_step(blk_ptr_addr, ptr(edges_b), ptr(contrib_in), ptr(partial), ptr(inv_deg),
+                                               ptr(rank_out), ptr(contrib_out), ptr(peer_contrib), nranks, row_begin,
+                                               nrows, num_nodes, int(first), int(last), stream_ptr()),
+          "cme_pagerank_block_step")
+    _count()
+
+
 def pagerank_gen_edges(edges: torch.Tensor, edge_begin: int, num_nodes: int, seed: int) -> None:
     check(device_lib().cme_pagerank_gen_edges(ptr(edges), edge_begin, edges.numel(), num_nodes,
                                               seed, stream_ptr()), "cme_pagerank_gen_edges")

@@ -26,8 +26,37 @@ def edge_balanced_cuts(row_ptr: np.ndarray, world: int) -> list[int]:
     return cuts
 
 
+def column_blocked_csr(row_ptr_local: torch.Tensor, edges: torch.Tensor, num_nodes: int, block_nodes: int):
+    """Regroup a CSR slice by L2-sized blocks of SOURCE nodes: returns (blk_ptr, edges_b, nblocks) with
+    blk_ptr int32 [nblocks * nrows + 1] and the edges of (block b, row i) at
+    edges_b[blk_ptr[b * nrows + i] : blk_ptr[b * nrows + i + 1]], in their original relative order.
+    Done once per graph on the device, outside every timed loop (torch sort / scan: set-up work)."""
+    nrows = row_ptr_local.numel() - 1
+    nb = (num_nodes + block_nodes - 1) // block_nodes
+    E = edges.numel()
+    if E >= 2**31:
+        raise ValueError("column_blocked_csr: a slice holds at most 2^31 - 1 edges")
+    deg = (row_ptr_local[1:] - row_ptr_local[:-1]).to(torch.int64)
+    rows = torch.repeat_interleave(torch.arange(nrows, device=edges.device, dtype=torch.int64), deg)
+    # uint32 node ids held in an int32 tensor: widen before dividing
+    src = edges.to(torch.int64) & 0xFFFFFFFF
+    key = (src // block_nodes) * nrows + rows
+    del src, rows, deg
+    order = torch.argsort(key, stable=True)
+    edges_b = edges[order].contiguous()
+    del order
+    counts = torch.bincount(key, minlength=nb * nrows)
+    del key
+    blk_ptr = torch.zeros(nb * nrows + 1, dtype=torch.int32, device=edges.device)
+    blk_ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+    return blk_ptr, edges_b, nb
+
+
 class PageRankShards:
-    def __init__(self, num_nodes: int, avg_edges: int, info: DistInfo, seed: int = 1):
+    def __init__(self, num_nodes: int, avg_edges: int, info: DistInfo, seed: int = 1,
+                 block_nodes: int | None = None):
+        """block_nodes: source nodes per block of the column-blocked propagation (None = automatic:
+        8 M nodes = 32 MB of contributions once the vector no longer fits in L2; 0 = never)."""
         self.n, self.avg, self.info = num_nodes, avg_edges, info
         row_ptr, _, inv_deg = host.pagerank_graph(num_nodes, avg_edges, seed, with_edges=False)
         m = int(row_ptr[-1])
@@ -47,6 +76,17 @@ class PageRankShards:
         self.pads = SymmetricTensor(1024, torch.int32, info)
         self.pads_dev = self.pads.ptr_table_dev()
         self.num_edges_total = m
+        if block_nodes is None:
+            block_nodes = (8 << 20) if num_nodes > (16 << 20) else 0
+        self.block_nodes = block_nodes
+        self.blocked = None
+        if block_nodes and block_nodes < num_nodes:
+            local_ptr = self.row_ptr - int(row_ptr[self.row_begin])
+            blk_ptr, edges_b, nb = column_blocked_csr(local_ptr, self.edges[: e1 - e0], num_nodes, block_nodes)
+            self.blocked = (blk_ptr, edges_b, nb)
+            self.partial = torch.zeros(max(self.row_end - self.row_begin, 1), dtype=torch.float32, device=d)
+            self.edges = None                       # the regrouped copy replaces the plain edge list
+            torch.cuda.empty_cache()
 
     def run(self, iterations: int) -> None:
         info, n = self.info, self.n
@@ -56,13 +96,25 @@ class PageRankShards:
             dev.peer_barrier(self.pads_dev, info.rank, info.world, 3, 0)
         # row_ptr / edges are local arrays indexed with global offsets: shift the base addresses
         rp = self.row_ptr.data_ptr() - self.row_begin * 8
-        ed = self.edges.data_ptr() - self.edge_base * 4
+        ed = self.edges.data_ptr() - self.edge_base * 4 if self.edges is not None else 0
+        nrows = self.row_end - self.row_begin
         for it in range(iterations):
             src, dst = it & 1, (it + 1) & 1
-            dev.pagerank_step(rp, ed, self.contrib[src].tensor, self.inv_deg, self.rank_out,
-                              self.contrib[dst].tensor, self.row_begin, self.row_end, n,
-                              peer_contrib=self.peer_tables[dst] if info.world > 1 else None,
-                              nranks=info.world)
+            if self.blocked is not None:
+                # one pass per block of source nodes: the gathers of a pass stay inside a window of
+                # the contribution vector that fits in L2
+                blk_ptr, edges_b, nb = self.blocked
+                for b in range(nb):
+                    dev.pagerank_block_step(blk_ptr.data_ptr() + 4 * b * nrows, edges_b, self.contrib[src].tensor,
+                                            self.partial, self.inv_deg, self.rank_out, self.contrib[dst].tensor,
+                                            self.row_begin, nrows, n, first=b == 0, last=b == nb - 1,
+                                            peer_contrib=self.peer_tables[dst] if info.world > 1 else None,
+                                            nranks=info.world)
+            else:
+                dev.pagerank_step(rp, ed, self.contrib[src].tensor, self.inv_deg, self.rank_out,
+                                  self.contrib[dst].tensor, self.row_begin, self.row_end, n,
+                                  peer_contrib=self.peer_tables[dst] if info.world > 1 else None,
+                                  nranks=info.world)
             if info.world > 1:
                 dev.peer_barrier(self.pads_dev, info.rank, info.world, 3, 0)
         self.last = iterations & 1

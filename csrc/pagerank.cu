@@ -61,6 +61,44 @@ propagate_kernel(const int64_t* __restrict__ row_ptr, const uint32_t* __restrict
     }
 }
 
+// ---- column-blocked propagation (graphs whose contribution vector does not fit in L2) ----------
+// ncu on 64 M nodes: the plain kernel runs at 95 % of the DRAM copy rate and still takes 8.6 ms per
+// iteration, because every random 4-byte gather costs a 64-byte HBM fetch (3 DRAM sectors per
+// edge).  Here the edges are regrouped once, outside the timed loop, by the L2-sized block of
+// source nodes they point into (a CSR per block, block-major); one pass per block then gathers
+// from a window of the contribution vector that stays in L2, and the row sums travel between the
+// passes in `partial`.  Terms are added in (block, original order) instead of original order.
+__global__ void __launch_bounds__(256)
+propagate_block_kernel(const int32_t* __restrict__ blk_ptr, const uint32_t* __restrict__ edges_b,
+                       const float* __restrict__ contrib_in, float* __restrict__ partial,
+                       const float* __restrict__ inv_deg, float* __restrict__ rank_out,
+                       float* __restrict__ contrib_out, float* const* __restrict__ peer_contrib, int nranks,
+                       int64_t row_begin, int64_t nrows, float base, int first, int last) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride) {
+        int j = blk_ptr[i];
+        const int end = blk_ptr[i + 1];
+        float sum = first ? 0.f : partial[i];
+        for (; j + 2 <= end; j += 2) {
+            const float c0 = __ldg(contrib_in + edges_b[j]), c1 = __ldg(contrib_in + edges_b[j + 1]);
+            sum += c0;
+            sum += c1;
+        }
+        if (j < end) sum += __ldg(contrib_in + edges_b[j]);
+        if (!last) {
+            partial[i] = sum;
+            continue;
+        }
+        const int64_t g = row_begin + i;
+        const float r = base + 0.5f * sum;
+        rank_out[g] = r;
+        const float c = r * inv_deg[g];
+        if (nranks <= 1) contrib_out[g] = c;
+        else
+            for (int p = 0; p < nranks; ++p) peer_contrib[p][g] = c;
+    }
+}
+
 // One row of the propagation: gathers in edge order, four in flight.  CG: contrib is read
 // through L2 only (the persistent kernel below re-reads a buffer another SM rewrote two
 // iterations earlier; an L1 line could be stale).
@@ -183,6 +221,25 @@ int cme_pagerank_iterate(const int64_t* row_ptr, const uint32_t* edges, const fl
                     (void*)&contrib_b, (void*)&rank_out, (void*)&iterations, (void*)&num_nodes, (void*)&base};
     CME_CUDA(cudaLaunchCooperativeKernel((const void*)iterate_persistent_kernel, dim3(grid), dim3(256), args, 0,
                                          cme::as_stream(stream)));
+    return 0;
+}
+
+int cme_pagerank_block_step(const int32_t* blk_ptr, const uint32_t* edges_b, const float* contrib_in, float* partial,
+                            const float* inv_deg, float* rank_out, float* contrib_out, float* const* peer_contrib,
+                            int nranks, int64_t row_begin, int64_t nrows, int64_t num_nodes, int first, int last,
+                            void* stream) {
+    CME_CHECK_ARG(blk_ptr && edges_b && contrib_in && partial && inv_deg && rank_out,
+                  "cme_pagerank_block_step: null buffer");
+    CME_CHECK_ARG(0 <= row_begin && nrows >= 0 && row_begin + nrows <= num_nodes, "cme_pagerank_block_step: bad row range");
+    CME_CHECK_ARG(!last || (nranks <= 1 ? contrib_out != nullptr : peer_contrib != nullptr),
+                  "cme_pagerank_block_step: missing contrib destination");
+    if (nrows == 0) return 0;
+    const float base = 0.5f / (float)num_nodes;
+    const int grid = cme::stride_grid(nrows, 256, 8, 8);
+    propagate_block_kernel<<<grid, 256, 0, cme::as_stream(stream)>>>(
+        blk_ptr, edges_b, contrib_in, partial, inv_deg, rank_out, contrib_out, peer_contrib, nranks, row_begin,
+        nrows, base, first, last);
+    CME_LAUNCH_CHECK();
     return 0;
 }
 

@@ -54,12 +54,19 @@ int cme_pagerank_step(const int64_t* row_ptr, const uint32_t* edges, const float
                       const float* inv_deg, float* rank_out, float* contrib_out,
                       float* const* peer_contrib, int nranks, int64_t row_begin, int64_t row_end,
                       int64_t num_nodes, void* stream);
-/* `iterations` steps on one GPU, ping-ponging contrib_a / contrib_b (n floats each), all
- * launches issued back to back from native code with no host synchronisation
+/* `iterations` steps on one GPU, ping-ponging contrib_a / contrib_b (n floats each): the pre-scale
+ * and every iteration in ONE cooperative launch with grid barriers, no host synchronisation
  * (ref hw2code/pagerank.cu:59-136 device_graph_iterate).  rank_out gets the result. */
 int cme_pagerank_iterate(const int64_t* row_ptr, const uint32_t* edges, const float* rank0,
                          const float* inv_deg, float* contrib_a, float* contrib_b, float* rank_out,
                          int iterations, int64_t num_nodes, void* stream);
+/* One pass of the column-blocked propagation (graphs larger than L2): blk_ptr holds nrows + 1 offsets
+ * into edges_b for THIS block of source nodes (local rows), partial carries the row sums between
+ * passes; the last pass writes rank_out / the new contributions like cme_pagerank_step. */
+int cme_pagerank_block_step(const int32_t* blk_ptr, const uint32_t* edges_b, const float* contrib_in, float* partial,
+                            const float* inv_deg, float* rank_out, float* contrib_out, float* const* peer_contrib,
+                            int nranks, int64_t row_begin, int64_t nrows, int64_t num_nodes, int first, int last,
+                            void* stream);
 /* Device-side graph generator matching cmeh_pagerank_graph (same splitmix64). */
 int cme_pagerank_gen_edges(uint32_t* edges, int64_t edge_begin, int64_t edge_count,
                            int64_t num_nodes, uint64_t seed, void* stream);

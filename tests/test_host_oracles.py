@@ -148,3 +148,28 @@ def test_edge_balanced_row_partition(world):
     for r in range(world):
         edges = int(row_ptr[cuts[r + 1]] - row_ptr[cuts[r]])
         assert abs(edges - m / world) <= max_deg + 1, (r, edges, m / world)
+
+
+def test_column_blocked_csr_regroups_edges_by_source_block():
+    """The set-up step of the column-blocked PageRank: every (block, row) segment holds exactly the
+    row's edges that point into the block, in their original order."""
+    import torch
+
+    from cme213_sp18_b200.parallel.pagerank_multi import column_blocked_csr
+
+    n, avg = 5000, 5
+    rp, edges, _ = host.pagerank_graph(n, avg, 3)
+    lo, hi = 1200, 4100                                   # a slice of rows, like one rank's shard
+    local_ptr = torch.from_numpy((rp[lo: hi + 1] - rp[lo]).astype(np.int64))
+    e = torch.from_numpy(edges[rp[lo]: rp[hi]].astype(np.int64).astype(np.int32))
+    block = 700
+    blk_ptr, edges_b, nb = column_blocked_csr(local_ptr, e, n, block)
+    assert nb == (n + block - 1) // block and blk_ptr.numel() == nb * (hi - lo) + 1
+    assert int(blk_ptr[-1]) == e.numel()
+    bp, eb = blk_ptr.numpy(), edges_b.numpy()
+    for i in (0, 1, 57, 1500, hi - lo - 1):
+        row = edges[rp[lo + i]: rp[lo + i + 1]]
+        for b in range(nb):
+            seg = eb[bp[b * (hi - lo) + i]: bp[b * (hi - lo) + i + 1]]
+            want = row[(row // block) == b]
+            assert np.array_equal(seg.astype(np.int64), want.astype(np.int64))
