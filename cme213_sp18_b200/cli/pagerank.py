@@ -47,8 +47,8 @@ def main(argv=None) -> int:
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--block-nodes", type=int, default=None,
-                    help="source nodes per block of the column-blocked propagation (default: 8 M once the "
-                         "graph has more than 16 M nodes; 0 = plain CSR)")
+                    help="source nodes per block of the column-blocked propagation (default: 16 M once the "
+                         "graph has more than 24 M nodes; 0 = plain CSR)")
     ap.add_argument("--l2-fetch", type=int, default=0, choices=[0, 32, 64, 128],
                     help="L2 fetch granularity in bytes for the run (0 = leave the driver's default of 64); "
                          "measured: 32 changes nothing at 64 M nodes (51.79 vs 51.83 ms), HBM fetches 64 bytes anyway")

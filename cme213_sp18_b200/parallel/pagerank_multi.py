@@ -56,7 +56,10 @@ class PageRankShards:
     def __init__(self, num_nodes: int, avg_edges: int, info: DistInfo, seed: int = 1,
                  block_nodes: int | None = None):
         """block_nodes: source nodes per block of the column-blocked propagation (None = automatic:
-        8 M nodes = 32 MB of contributions once the vector no longer fits in L2; 0 = never)."""
+        16 M nodes = 64 MB of contributions once the vector no longer fits in L2; 0 = never).
+        Measured at 64 M nodes, 8 edges per node, six iterations on one B200: plain CSR 51.8 ms,
+        16 blocks of 4 M nodes 34.4, 8 blocks of 8 M 22.1, 4 blocks of 16 M 18.9 (every pass re-reads
+        the row offsets and the partial sums, so fewer, larger blocks win while a block fits in L2)."""
         self.n, self.avg, self.info = num_nodes, avg_edges, info
         row_ptr, _, inv_deg = host.pagerank_graph(num_nodes, avg_edges, seed, with_edges=False)
         m = int(row_ptr[-1])
@@ -77,7 +80,7 @@ class PageRankShards:
         self.pads_dev = self.pads.ptr_table_dev()
         self.num_edges_total = m
         if block_nodes is None:
-            block_nodes = (8 << 20) if num_nodes > (16 << 20) else 0
+            block_nodes = (16 << 20) if num_nodes > (24 << 20) else 0
         self.block_nodes = block_nodes
         self.blocked = None
         if block_nodes and block_nodes < num_nodes:
