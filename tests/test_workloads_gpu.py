@@ -89,6 +89,15 @@ def test_mlp_cli_stream_mode(tmp_path):
     assert prec > 0.85, r.stdout
 
 
+def test_pagerank_column_blocked_matches_host(tmp_path):
+    """The column-blocked propagation (graphs larger than L2) on a graph small enough for the host
+    oracle: six blocks of 50 000 source nodes, 100 ULP (ref hw2code/main_q2.cu:28)."""
+    r = run_module("cme213_sp18_b200.cli.pagerank", "--nodes", "300000", "--avg", "6", "--block-nodes", "50000",
+                   cwd=tmp_path)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "6 column blocks" in r.stdout and "(ok)" in r.stdout, r.stdout[-2000:]
+
+
 @pytest.mark.multigpu
 @pytest.mark.timeout(900)
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -115,6 +124,9 @@ def test_multi_gpu_heat_slabs_and_pagerank_match_host(tmp_path, world):
                        nproc=world, port=29601 + world)
         assert p.returncode == 0 and f"ranks={world}" in p.stdout and "ok" in p.stdout, \
             p.stdout[-3000:] + p.stderr[-3000:]
+    p = run_module("cme213_sp18_b200.cli.pagerank", "--nodes", str(1 << 20), "--avg", "8", "--block-nodes", str(1 << 18),
+                   cwd=tmp_path, nproc=world, port=29611 + world)
+    assert p.returncode == 0 and "4 column blocks" in p.stdout and "(ok)" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
 
 
 def test_cpp_example_trains_without_python():
