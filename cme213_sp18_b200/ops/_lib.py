@@ -70,6 +70,7 @@ _DEV_SIGS = {
     "cme_mlp_stage_recast": [P, P, P, c_i64, c_int, c_int, P, P, c_int, P, c_int, c_int, P],
     "cme_update_slice": [c_i64, c_i64, c_int, c_int, P],
     "cme_mlp_dw1_scratch_bytes": [],
+    "cme_mlp_dw1_plan_query": [c_i64, c_int, c_int, P],
     "cme_mlp_bwd_tail_scratch_floats": [c_int],
     "cme_mlp_bwd_tail_det": [P, P, P, P, P, c_int, c_i64, c_int, c_int, c_int, P, P],
     "cme_mlp_fwd_fused_ok": [c_i64, c_int],

@@ -1722,6 +1722,33 @@ static uint32_t* dw1_default_scratch() {
     return p;
 }
 
+/* How cme_mlp_dw1 / cme_mlp_dw1_update would tile a dW1 product of `rows` samples (no launch, no
+ * GPU needed): out = {pair path (0/1), row tiles, column tiles, column-tile width, k-split, CTAs}.
+ * The same arithmetic as dw1_launch; exists so the tiling rules can be tested and inspected. */
+int cme_mlp_dw1_plan_query(int64_t rows, int K, int H, int out[6]) {
+    CME_CHECK_ARG(out && rows > 0 && K > 0 && H > 0, "cme_mlp_dw1_plan_query: bad argument");
+    const int unit_rows = ((H + 63) / 64 * 64) >= 512 ? 256 : 128;
+    const int m_tiles = (H + BM - 1) / BM;
+    const int kb_total = (int)((rows + BK - 1) / BK);
+    if (H >= 512 && K >= 256 && kb_total >= 16 && unit_rows == 256) {
+        const int m2 = (H + 255) / 256, n2 = (K + 255) / 256, npairs = cme::sm_count() / 2;
+        const int ks = choose_ksplit_pairs(m2 * n2, kb_total, npairs);
+        const long long items = (long long)m2 * n2 * ks;
+        out[0] = 1, out[1] = m2, out[2] = n2, out[3] = 256, out[4] = ks;
+        out[5] = 2 * (int)std::min<long long>(items, npairs);
+        return 0;
+    }
+    int bn_cap = 256, ks_small = 0;
+    if ((long long)m_tiles * ((K + 255) / 256) * 16 <= cme::sm_count())
+        choose_small_tiling(m_tiles, K, kb_total, cme::sm_count(), &bn_cap, &ks_small);
+    const int n_tiles = (K + bn_cap - 1) / bn_cap;
+    const int BN = ((K + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    const int ks = ks_small > 0 ? ks_small : choose_ksplit(m_tiles * n_tiles, kb_total, cme::sm_count());
+    out[0] = 0, out[1] = m_tiles, out[2] = n_tiles, out[3] = BN, out[4] = ks;
+    out[5] = (int)std::min<long long>((long long)m_tiles * n_tiles * ks, cme::sm_count());
+    return 0;
+}
+
 size_t cme_mlp_dw1_scratch_bytes(void) { return sizeof(uint32_t) * (kDwPartWords + kDwUnitWords); }
 
 int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,

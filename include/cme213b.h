@@ -285,6 +285,9 @@ int cme_f32_to_bf16_2d(const float* src, int ld_src, void* dst_bf16, int ld_dst,
  * e.g. another large kernel shares the GPU); with NULL the kernel traps instead. */
 int cme_mlp_dw1(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
                 int ldh, int ldg, void* stream);
+/* Tiling of a dW1 product of `rows` samples without launching anything (works without a GPU; 148 SMs
+ * assumed then): out = {CTA-pair path 0/1, row tiles, column tiles, column-tile width, k-split, CTAs}. */
+int cme_mlp_dw1_plan_query(int64_t rows, int K, int H, int out[6]);
 size_t cme_mlp_dw1_scratch_bytes(void);
 int cme_mlp_dw1_sync(const void* dZ1, const void* X, float* gW1, int64_t rows, int K, int H, int ldx,
                      int ldh, int ldg, void* scratch, uint32_t* const* pads, int nranks, int unit_rows,

@@ -153,3 +153,48 @@ def test_flat_vector_layout_agrees_between_python_and_c():
         assert lay["n_total"] % 4 == 0 and lay["o_b2"] % 4 == 0
     p.ldx -= 64
     assert lib.cme_mlp_layout(C.addressof(p), out) == -1 and "do not fit" in _err(lib)
+
+
+def test_dw1_tiling_rules():
+    """The tiling of the dW1 GEMM as the library would launch it (148 SMs assumed without a GPU).
+    The rules were fitted to measurements (see choose_ksplit_pairs / choose_small_tiling in
+    csrc/gemm_tc.cu); this pins them so that a change shows up in review."""
+    lib = _lib.device_lib()
+
+    def plan(rows, K, H):
+        out = (C.c_int * 6)()
+        assert lib.cme_mlp_dw1_plan_query(rows, K, H, out) == 0, _err(lib)
+        return dict(zip(("pairs", "m_tiles", "n_tiles", "bn", "ksplit", "ctas"), out))
+
+    # flagship: 784-8192-10.  CTA pairs, 256 x 256 tiles, and no k-split once the 128 tiles cover
+    # half the machine, at 65536 rows on one GPU as well as at 8192 rows per GPU on eight
+    for rows in (65536, 32768, 8192):
+        p = plan(rows, 785, 8192)
+        assert (p["pairs"], p["m_tiles"], p["n_tiles"], p["bn"], p["ksplit"]) == (1, 32, 4, 256, 1), (rows, p)
+        assert p["ctas"] == 148
+    # 784-1024-10: 16 tiles for 74 pairs -> a moderate split, every item resident
+    p = plan(8192, 785, 1024)
+    assert p["pairs"] == 1 and 1 <= p["ksplit"] <= 4 and p["m_tiles"] * p["n_tiles"] * p["ksplit"] <= 74, p
+    # 784-100-10: single-CTA kernel, narrow column tiles so that more SMs pull operands out of L2
+    p = plan(3200, 785, 100)
+    assert p["pairs"] == 0 and p["m_tiles"] == 1 and p["bn"] == 64 and p["n_tiles"] == 13 and 2 <= p["ksplit"] <= 3, p
+    p = plan(400, 785, 100)                       # one rank's share of the small config on 8 GPUs
+    assert p["pairs"] == 0 and p["bn"] == 64 and p["ksplit"] == 1, p
+    assert lib.cme_mlp_dw1_plan_query(0, 785, 100, (C.c_int * 6)()) == -1
+
+
+def test_fp64_entry_points_reject_bad_arguments():
+    lib = _lib.device_lib()
+    one = C.c_void_p(16)
+    tab = (C.c_void_p * 2)(16, 32)
+    assert lib.cme_allreduce_sgd_f64(tab, tab, one, 0, 2, 7, 0, 0, 0, 0.1, 0.0, 0, None) == -1
+    assert "even number of doubles" in _err(lib)
+    assert lib.cme_allreduce_sgd_f64(tab, tab, one, 2, 2, 8, 0, 0, 0, 0.1, 0.0, 0, None) == -1
+    assert "rank 2 of 2" in _err(lib)
+    assert lib.cme_allreduce_sgd_f64(tab, tab, one, 0, 2, 8, 6, 4, 8, 0.1, 0.0, 0, None) == -1
+    assert "segment bounds" in _err(lib)
+    assert lib.cme_dgemm(0, 0, 4, 4, 4, 1.0, one, 2, one, 4, 0.0, one, 4, None) == -1
+    assert "leading dimension" in _err(lib)
+    assert lib.cme_dgemm(0, 0, 0, 4, 4, 1.0, None, 1, None, 4, 0.0, None, 1, None) == 0      # empty product: nothing to do
+    assert lib.cme_pagerank_block_step(one, one, one, one, one, one, one, None, 1, 8, 4, 10, 1, 1, None) == -1
+    assert "row range" in _err(lib)
