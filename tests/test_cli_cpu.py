@@ -85,3 +85,25 @@ def test_tracer_and_cli_trace_file(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     names = [e["name"] for e in json.loads((tmp_path / "run.json").read_text())["traceEvents"]]
     assert names.count("serial epoch") == 2 and "parallel_train" in names
+
+
+def test_bench_contract_on_a_box_without_a_gpu():
+    """bench.py's reference arm must print ONE JSON line and exit 0 even where it cannot run; the
+    "ours" arm must fail loudly (no silent CPU fallback for a GPU benchmark)."""
+    import json
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("this is the no-GPU contract")
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and "unavailable" in line
+    r = subprocess.run([sys.executable, str(root / "bench.py"), "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0                       # no GPU: refuse, do not pretend
