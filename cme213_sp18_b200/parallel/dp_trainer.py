@@ -313,8 +313,8 @@ class NativeFeeder:
     """Same job as StreamingFeeder with the loop in C++ (csrc/mlp_runtime.cu): one call queues
     every step of the run (H2D on a copy stream, one CUDA graph per step, loss read-back), so
     the Python interpreter is not on the per-step path at all.  The step inside is
-    cme_mlp_step_ex, the same schedule MLPEngineBF16 issues (side-stream memset, bucketed
-    overlap of the first half of the W1 reduction with the rest of the backward pass)."""
+    cme_mlp_step_ex, the same schedule MLPEngineBF16 issues (six launches, the gradient
+    all-reduce + SGD inside the dW1 GEMM)."""
 
     def __init__(self, engine, D: int, graph: bool = True):
         from ..ops import device as dev

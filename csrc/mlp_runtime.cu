@@ -10,7 +10,7 @@
 //                   one of two device staging slots
 //   compute stream  one CUDA graph per distinct row count holding the whole step
 //                   (cme_mlp_step_ex in its indirect form: staging, forward, backward, the
-//                   streaming all-reduce + SGD on a side stream next to the dW1 GEMM, re-cast;
+//                   streaming all-reduce + SGD inside the dW1 GEMM;
 //                   the staging slot, labels, lr, reg and scale are read from CmeStepArgs in
 //                   device memory, written by a one-thread kernel before each replay, so a
 //                   learning-rate schedule or a long dataset never adds graphs)

@@ -353,10 +353,8 @@ typedef struct CmeMlpPlan {
     float* dz2;
     int32_t* pred;
     uint32_t* const* pads_dev;
-    /* overlap != 0: the streaming update runs on the side stream next to the dW1 GEMM (needs a
-     * side stream); 0: after it, on the same stream (use this under tools that serialise kernels,
-     * e.g. ncu or compute-sanitizer: a kernel that waits for flags cannot start before the kernel
-     * that raises them there).  use_mc: reduce through the NVSwitch multicast mappings below
+    /* overlap != 0: the streaming update runs INSIDE the dW1 GEMM (four extra warps per CTA);
+     * 0: as a kernel of its own after it, on the same stream.  use_mc: reduce through the NVSwitch multicast mappings below
      * instead of peer loads. */
     int overlap, use_mc;
     const float* grads_mc;
@@ -387,9 +385,10 @@ typedef struct CmeMlpPlan {
  * scale = 1 / (global samples in the minibatch); loss_sum (may be NULL) += cross-entropy.
  * The C++ counterpart of one iteration of parallel_train's loop
  * (ref fpcode/neural_network.cpp:484-541).  cme_mlp_step issues everything on `stream`;
- * cme_mlp_step_ex also takes a side stream and 4 cudaEvent_t (disable-timing is fine) and
- * runs the update kernel there, next to the dW1 GEMM that feeds it; both are capturable
- * into a CUDA graph from `stream`.  With several ranks every rank must issue the same steps. */
+ * cme_mlp_step_ex also takes a side stream and 4 cudaEvent_t (disable-timing is fine), used only
+ * by models that still zero the tail of the gradient vector (hidden width not a multiple of 256:
+ * the memset then hides under the forward GEMM); both are capturable into a CUDA graph from
+ * `stream`.  With several ranks every rank must issue the same steps. */
 int cme_mlp_step(const CmeMlpPlan* plan, const uint8_t* x_u8, const int32_t* labels, int64_t rows,
                  float lr, float reg, float scale, float* loss_sum, void* stream);
 /* x_u8 == NULL selects the indirect form: inputs, labels, lr, reg and scale are read on the
