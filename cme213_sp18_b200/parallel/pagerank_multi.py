@@ -11,6 +11,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
+from ..models.pagerank import column_blocked_csr  # noqa: F401  (re-exported)
 from ..ops import device as dev
 from ..ops import host
 from .dist import DistInfo, SymmetricTensor
@@ -24,32 +25,6 @@ def edge_balanced_cuts(row_ptr: np.ndarray, world: int) -> list[int]:
     cuts = [int(np.searchsorted(row_ptr, m * r // world)) for r in range(world)] + [n]
     cuts[0] = 0
     return cuts
-
-
-def column_blocked_csr(row_ptr_local: torch.Tensor, edges: torch.Tensor, num_nodes: int, block_nodes: int):
-    """Regroup a CSR slice by L2-sized blocks of SOURCE nodes: returns (blk_ptr, edges_b, nblocks) with
-    blk_ptr int32 [nblocks * nrows + 1] and the edges of (block b, row i) at
-    edges_b[blk_ptr[b * nrows + i] : blk_ptr[b * nrows + i + 1]], in their original relative order.
-    Done once per graph on the device, outside every timed loop (torch sort / scan: set-up work)."""
-    nrows = row_ptr_local.numel() - 1
-    nb = (num_nodes + block_nodes - 1) // block_nodes
-    E = edges.numel()
-    if E >= 2**31:
-        raise ValueError("column_blocked_csr: a slice holds at most 2^31 - 1 edges")
-    deg = (row_ptr_local[1:] - row_ptr_local[:-1]).to(torch.int64)
-    rows = torch.repeat_interleave(torch.arange(nrows, device=edges.device, dtype=torch.int64), deg)
-    # uint32 node ids held in an int32 tensor: widen before dividing
-    src = edges.to(torch.int64) & 0xFFFFFFFF
-    key = (src // block_nodes) * nrows + rows
-    del src, rows, deg
-    order = torch.argsort(key, stable=True)
-    edges_b = edges[order].contiguous()
-    del order
-    counts = torch.bincount(key, minlength=nb * nrows)
-    del key
-    blk_ptr = torch.zeros(nb * nrows + 1, dtype=torch.int32, device=edges.device)
-    blk_ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
-    return blk_ptr, edges_b, nb
 
 
 class PageRankShards:
