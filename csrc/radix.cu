@@ -61,48 +61,54 @@ radix_histogram(const uint32_t* __restrict__ keys, size_t n, int shift, uint32_t
     histo[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of `count` uint32 values by one block of 1024 threads
+// Exclusive scan of `count` uint32 values by one block of 1024 threads.  Every warp owns one
+// contiguous segment and walks it 128 values at a time with shuffles only (its running total stays
+// in a register), the 32 segment totals are scanned once, and a second sweep adds each segment's
+// offset.  The first version synchronised the whole block four times per 4096 values: 64 rounds
+// per pass for 4 M keys, about 110 us of the 170 us a pass took.
 __global__ void __launch_bounds__(1024) radix_scan(uint32_t* __restrict__ data, size_t count) {
     __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    // each thread scans 4 consecutive values so a pass covers 4096 entries
-    for (size_t base = 0; base < count; base += 4096) {
-        const size_t i = base + (size_t)threadIdx.x * 4;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t seg = ((count + 31) / 32 + 127) / 128 * 128;
+    const size_t lo = min(count, (size_t)warp * seg), hi = min(count, lo + seg);
+    uint32_t carry = 0;
+#pragma unroll 4
+    for (size_t base = lo; base < hi; base += 128) {
+        const size_t i = base + (size_t)lane * 4;
         uint32_t v[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) v[k] = (i + k < count) ? data[i + k] : 0;
+        for (int k = 0; k < 4; ++k) v[k] = (i + k < hi) ? data[i + k] : 0;
         const uint32_t tsum = v[0] + v[1] + v[2] + v[3];
         uint32_t inc = tsum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if ((threadIdx.x & 31) >= o) inc += t;
+            if (lane >= o) inc += t;
         }
-        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            uint32_t w = warp_tot[threadIdx.x];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-                if (threadIdx.x >= o) w += t;
-            }
-            warp_tot[threadIdx.x] = w;
-        }
-        __syncthreads();
-        const uint32_t c0 = carry;
-        uint32_t run = c0 + ((threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0) + inc - tsum;
+        uint32_t run = carry + inc - tsum;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            if (i + k < count) data[i + k] = run;
+            if (i + k < hi) data[i + k] = run;
             run += v[k];
         }
-        __syncthreads();
-        if (threadIdx.x == 0) carry = c0 + warp_tot[31];
-        __syncthreads();
+        carry += __shfl_sync(0xffffffffu, inc, 31);
     }
+    if (lane == 0) warp_tot[warp] = carry;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t mine = warp_tot[lane];
+        uint32_t w = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        warp_tot[lane] = w - mine;                 // exclusive: what precedes this warp's segment
+    }
+    __syncthreads();
+    const uint32_t off = warp_tot[warp];
+    if (off != 0)
+        for (size_t i = lo + lane; i < hi; i += 32) data[i] += off;
 }
 
 // Stable scatter: keys of a tile are ranked round by round (round, warp, lane
