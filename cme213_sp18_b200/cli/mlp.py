@@ -40,6 +40,9 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("-p", dest="print_every", type=int, default=0)
     ap.add_argument("-s", dest="run_seq", action="store_true")
     ap.add_argument("-d", dest="debug", action="store_true")
+    ap.add_argument("--serial-backend", default="torch", choices=["torch", "native"],
+                    help="-s: run the sequential trainer on torch CPU tensors (the oracle) or in the C++/OpenMP "
+                         "host library (no debug dumps there)")
     ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp64"])
     ap.add_argument("--comm", default="fused", choices=["fused", "p2p", "mc", "nccl"])
     ap.add_argument("--data-mode", default="owner", choices=["owner", "sharded", "stream"],
@@ -106,8 +109,11 @@ def main(argv=None) -> int:
     if rank0 and args.run_seq:
         print("Start Sequential Training")
         t0 = time.perf_counter()
-        M.train(seq_nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
-                args.print_every, args.debug, outdir=str(out / "CPUmats"), tracer=cpu_tracer)
+        if args.serial_backend == "native" and not args.debug:
+            M.train_native(seq_nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, args.print_every)
+        else:
+            M.train(seq_nn, x_train, l_train, args.lr, args.reg, args.epochs, args.batch, False,
+                    args.print_every, args.debug, outdir=str(out / "CPUmats"), tracer=cpu_tracer)
         print(f"Time for Sequential Training: {time.perf_counter() - t0} seconds")
         prec = M.precision(M.predict(seq_nn, x_dev), l_dev)
         print(f"Precision on validation set for sequential training = {prec}")

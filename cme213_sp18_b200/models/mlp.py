@@ -237,6 +237,27 @@ def train(nn: NeuralNetwork, X: torch.Tensor, labels: torch.Tensor, learning_rat
     return {"iterations": it, "losses": losses}
 
 
+def train_native(nn: NeuralNetwork, X: torch.Tensor, labels: torch.Tensor, learning_rate: float = 0.001,
+                 reg: float = 0.0, epochs: int = 1, batch_size: int = 800, print_every: int = -1,
+                 log=print) -> dict:
+    """The same serial schedule as train() run by the C++/OpenMP trainer of the host library
+    (csrc/host/mlp_cpu.cpp, ref fpcode/neural_network.cpp:219-279): no Python and no BLAS on the
+    per-step path.  `nn` is updated in place; returns {'iterations', 'losses'}."""
+    from ..ops import host
+
+    w = [nn.W[0].contiguous().numpy().copy(), nn.b[0].contiguous().numpy().copy(),
+         nn.W[1].contiguous().numpy().copy(), nn.b[1].contiguous().numpy().copy()]
+    it, losses = host.mlp_train(X.to(F64).contiguous().numpy(), labels.to(torch.int32).contiguous().numpy(), *w,
+                                learning_rate, reg, epochs, batch_size, loss_every=max(print_every, 0))
+    nn.W = [torch.from_numpy(w[0]), torch.from_numpy(w[2])]
+    nn.b = [torch.from_numpy(w[1]), torch.from_numpy(w[3])]
+    out = [(i * print_every, float(v)) for i, v in enumerate(losses)] if print_every > 0 else []
+    num_batches = (X.shape[0] + batch_size - 1) // batch_size
+    for i, v in out:
+        log(f"Loss at iteration {i} of epoch {i // max(num_batches, 1)}/{epochs} = {v}")
+    return {"iterations": it, "losses": out}
+
+
 def split_train_dev(X: torch.Tensor, labels: torch.Tensor, dev_fraction: float = 0.1):
     """Last 10 % of the samples are the dev set (ref fpcode/main.cpp:197-204)."""
     n = X.shape[0]

@@ -96,6 +96,8 @@ _DEV_RESTYPES = {"cme_radix_scratch_bytes": c_size_t, "cme_mlp_dw1_scratch_bytes
 
 _HOST_SIGS = {
     "cmeh_num_threads": [],
+    "cmeh_mlp_train": [P, P, c_i64, c_int, c_int, c_int, P, P, P, P, c_double, c_double, c_int, c_int, c_int, P, c_i64],
+    "cmeh_mlp_forward": [P, c_i64, c_int, c_int, c_int, P, P, P, P, P, P],
     "cmeh_parity_sum_serial": [P, c_size_t, P, P],
     "cmeh_parity_sum_omp": [P, c_size_t, c_int, P, P],
     "cmeh_radix_block_histograms": [P, c_size_t, c_u32, c_u32, c_u32, c_size_t, P],
@@ -117,7 +119,7 @@ _HOST_SIGS = {
     "cmeh_idx_info": [C.c_char_p, P, P],
     "cmeh_idx_read": [C.c_char_p, c_i64, c_i64, P],
 }
-_HOST_RESTYPES = {"cmeh_max_ulp_f32": c_i64, "cmeh_max_ulp_f64": c_i64, "cmeh_idx_info": c_i64,
+_HOST_RESTYPES = {"cmeh_mlp_train": c_i64, "cmeh_max_ulp_f32": c_i64, "cmeh_max_ulp_f64": c_i64, "cmeh_idx_info": c_i64,
                   "cmeh_idx_read": c_i64}
 
 

@@ -201,3 +201,43 @@ def idx_read(path, first_item: int, num_items: int, item_bytes: int) -> np.ndarr
     if got != out.size:
         raise ValueError(f"{path}: short or bad IDX read (code {got})")
     return out
+
+
+# ------------------------------------------------------------------ fpcode: native serial trainer
+def mlp_train(X: np.ndarray, labels: np.ndarray, W1: np.ndarray, b1: np.ndarray, W2: np.ndarray, b2: np.ndarray,
+              lr: float, reg: float, epochs: int, batch: int, loss_every: int = 0):
+    """The serial fp64 trainer in C++/OpenMP (ref fpcode/neural_network.cpp:219-279).  X [N, D]
+    float64, labels [N]; W1 [H, D], b1 [H], W2 [C, H], b2 [C] are float64 C-contiguous arrays
+    updated IN PLACE.  Returns (iterations, losses) with one loss per loss_every iterations."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    for a in (W1, b1, W2, b2):
+        if a.dtype != np.float64 or not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("mlp_train: the weights must be float64 C-contiguous arrays (updated in place)")
+    N, D = X.shape
+    H, Cn = W1.shape[0], W2.shape[0]
+    if W1.shape != (H, D) or b1.shape != (H,) or W2.shape != (Cn, H) or b2.shape != (Cn,) or labels.shape != (N,):
+        raise ValueError("mlp_train: shapes do not fit together")
+    nb = (N + batch - 1) // batch
+    cap = (epochs * nb + loss_every - 1) // loss_every if loss_every > 0 else 0
+    losses = np.zeros(max(cap, 1), dtype=np.float64)
+    it = host_lib().cmeh_mlp_train(np_ptr(X), np_ptr(labels), N, D, H, Cn, np_ptr(W1), np_ptr(b1), np_ptr(W2), np_ptr(b2),
+                                   lr, reg, epochs, batch, loss_every, np_ptr(losses), cap)
+    if it < 0:
+        raise ValueError("cmeh_mlp_train: bad argument" if it == -1 else "cmeh_mlp_train: a label is outside [0, C)")
+    return int(it), losses[:cap]
+
+
+def mlp_forward(X: np.ndarray, W1, b1, W2, b2, want_probs: bool = True):
+    """Forward pass of the native CPU model: (probs [N, C] or None, pred [N] int32)."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    N, D = X.shape
+    H, Cn = W1.shape[0], W2.shape[0]
+    probs = np.empty((N, Cn), dtype=np.float64) if want_probs else None
+    pred = np.empty(N, dtype=np.int32)
+    w = [np.ascontiguousarray(a, dtype=np.float64) for a in (W1, b1, W2, b2)]
+    rc = host_lib().cmeh_mlp_forward(np_ptr(X), N, D, H, Cn, *(np_ptr(a) for a in w),
+                                     np_ptr(probs) if want_probs else None, np_ptr(pred))
+    if rc != 0:
+        raise ValueError("cmeh_mlp_forward: bad argument")
+    return probs, pred

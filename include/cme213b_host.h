@@ -79,6 +79,22 @@ int cmeh_letter_histogram(const uint8_t* text, size_t n, size_t stride, size_t o
 int64_t cmeh_idx_info(const char* path, int32_t* magic, int64_t dims[3]);
 int64_t cmeh_idx_read(const char* path, int64_t first_item, int64_t num_items, uint8_t* dst);
 
+/* ---- fpcode: the serial fp64 trainer of the two-layer MLP (ref fpcode/neural_network.cpp:91-279) ----
+ * Row-major buffers: X [N][D] (one sample per row), labels [N] class ids, W1 [H][D], b1 [H],
+ * W2 [C][H], b2 [C]; the weights are updated in place.  epochs x ceil(N / batch) minibatches, the
+ * last one may be short; sigmoid hidden layer, softmax + cross-entropy, plain SGD with the L2 term
+ * reg * W in the weight gradients.  loss_every > 0: before the update of every loss_every-th
+ * iteration the minibatch loss (mean cross-entropy + 0.5 reg ||W||^2) is appended to losses
+ * (at most losses_cap values; losses may be NULL).  Returns the number of iterations, -1 on a bad
+ * argument, -2 on a label outside [0, C). */
+int64_t cmeh_mlp_train(const double* X, const int32_t* labels, int64_t N, int D, int H, int C, double* W1,
+                       double* b1, double* W2, double* b2, double lr, double reg, int epochs, int batch,
+                       int loss_every, double* losses, int64_t losses_cap);
+/* Forward pass: probs [N][C] (may be NULL) and arg-max classes pred [N] (may be NULL)
+ * (ref fpcode/neural_network.cpp:91-114, 159-169). */
+int cmeh_mlp_forward(const double* X, int64_t N, int D, int H, int C, const double* W1, const double* b1,
+                     const double* W2, const double* b2, double* probs, int32_t* pred);
+
 int cmeh_num_threads(void);
 
 #ifdef __cplusplus

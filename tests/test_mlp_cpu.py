@@ -189,3 +189,27 @@ def test_relu_and_cli_checkpoint_resume(tmp_path):
     r2 = subprocess.run(base + ["--resume", str(tmp_path / "ck.pt")], capture_output=True, text=True, cwd=tmp_path,
                         env=env, timeout=200)
     assert r2.returncode == 0 and "Resumed from" in r2.stdout, r2.stdout + r2.stderr
+
+
+def test_native_cpp_serial_trainer_matches_the_torch_oracle():
+    """csrc/host/mlp_cpu.cpp (C++/OpenMP, no BLAS) against models/mlp.train: same schedule, short
+    last batch included, weights and the printed losses equal to rounding
+    (ref fpcode/neural_network.cpp:219-279)."""
+    from cme213_sp18_b200.ops import host
+
+    x, lab = mnist.synthetic_mnist(1100, seed=3, pixel_max=1)          # 800 + 300: a short last batch
+    a, b = M.NeuralNetwork([784, 37, 10]), M.NeuralNetwork([784, 37, 10])
+    ra = M.train(a, x, lab, 0.3, 1e-3, 3, 800, print_every=2, log=lambda *_: None)
+    rb = M.train_native(b, x, lab, 0.3, 1e-3, 3, 800, print_every=2, log=lambda *_: None)
+    assert ra["iterations"] == rb["iterations"] == 6
+    for p, q in zip(a.W + a.b, b.W + b.b):
+        assert float((p - q).abs().max() / p.abs().max()) < 1e-12
+    assert len(ra["losses"]) == len(rb["losses"]) == 3
+    for (i, u), (j, v) in zip(ra["losses"], rb["losses"]):
+        assert i == j and abs(u - v) < 1e-12 * max(1.0, abs(u))
+    probs, pred = host.mlp_forward(x.double().numpy(), b.W[0].numpy(), b.b[0].numpy(), b.W[1].numpy(), b.b[1].numpy())
+    assert torch.equal(torch.from_numpy(pred).long(), M.predict(b, x))
+    assert abs(float(probs.sum(axis=1).max()) - 1.0) < 1e-12
+    with pytest.raises(ValueError):
+        host.mlp_train(x.double().numpy(), (lab + 20).numpy(), b.W[0].numpy().copy(), b.b[0].numpy().copy(),
+                       b.W[1].numpy().copy(), b.b[1].numpy().copy(), 0.1, 0.0, 1, 800)
