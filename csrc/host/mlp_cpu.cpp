@@ -22,11 +22,19 @@
 #include <omp.h>
 #endif
 
+// The build has no -march flag (the library must load on whatever CPU the GPU box has), so the three
+// kernels are compiled once per instruction set and picked at load time.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#define CME_MULTIVERSION __attribute__((target_clones("avx512f", "avx2,fma", "default")))
+#else
+#define CME_MULTIVERSION
+#endif
+
 namespace {
 
 // C[M][N] = A[M][K] * B[N][K]^T, all row-major.  4 x 4 register block, k innermost (both operands
 // are read along their contiguous dimension).
-void gemm_nt(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb,
+CME_MULTIVERSION void gemm_nt(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb,
              double* C, int64_t ldc) {
 #pragma omp parallel for schedule(static)
     for (int64_t i0 = 0; i0 < M; i0 += 4) {
@@ -39,14 +47,22 @@ void gemm_nt(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, cons
                              *a3 = A + (i0 + 3) * lda;
                 const double *b0 = B + (j0 + 0) * ldb, *b1 = B + (j0 + 1) * ldb, *b2 = B + (j0 + 2) * ldb,
                              *b3 = B + (j0 + 3) * ldb;
+                double s00 = 0, s01 = 0, s02 = 0, s03 = 0, s10 = 0, s11 = 0, s12 = 0, s13 = 0;
+                double s20 = 0, s21 = 0, s22 = 0, s23 = 0, s30 = 0, s31 = 0, s32 = 0, s33 = 0;
+                // sixteen dot products at once, vectorised along k (each sum becomes a vector of partial sums)
+#pragma omp simd reduction(+ : s00, s01, s02, s03, s10, s11, s12, s13, s20, s21, s22, s23, s30, s31, s32, s33)
                 for (int64_t k = 0; k < K; ++k) {
                     const double x0 = a0[k], x1 = a1[k], x2 = a2[k], x3 = a3[k];
                     const double y0 = b0[k], y1 = b1[k], y2 = b2[k], y3 = b3[k];
-                    acc[0][0] += x0 * y0; acc[0][1] += x0 * y1; acc[0][2] += x0 * y2; acc[0][3] += x0 * y3;
-                    acc[1][0] += x1 * y0; acc[1][1] += x1 * y1; acc[1][2] += x1 * y2; acc[1][3] += x1 * y3;
-                    acc[2][0] += x2 * y0; acc[2][1] += x2 * y1; acc[2][2] += x2 * y2; acc[2][3] += x2 * y3;
-                    acc[3][0] += x3 * y0; acc[3][1] += x3 * y1; acc[3][2] += x3 * y2; acc[3][3] += x3 * y3;
+                    s00 += x0 * y0; s01 += x0 * y1; s02 += x0 * y2; s03 += x0 * y3;
+                    s10 += x1 * y0; s11 += x1 * y1; s12 += x1 * y2; s13 += x1 * y3;
+                    s20 += x2 * y0; s21 += x2 * y1; s22 += x2 * y2; s23 += x2 * y3;
+                    s30 += x3 * y0; s31 += x3 * y1; s32 += x3 * y2; s33 += x3 * y3;
                 }
+                acc[0][0] = s00; acc[0][1] = s01; acc[0][2] = s02; acc[0][3] = s03;
+                acc[1][0] = s10; acc[1][1] = s11; acc[1][2] = s12; acc[1][3] = s13;
+                acc[2][0] = s20; acc[2][1] = s21; acc[2][2] = s22; acc[2][3] = s23;
+                acc[3][0] = s30; acc[3][1] = s31; acc[3][2] = s32; acc[3][3] = s33;
             } else {
                 for (int64_t i = 0; i < mi; ++i)
                     for (int64_t j = 0; j < nj; ++j) {
@@ -65,7 +81,7 @@ void gemm_nt(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, cons
 
 // C[M][N] = A[M][K] * B[K][N], all row-major: for every row of C, axpy over the rows of B
 // (j contiguous, vectorisable); rows of C are independent.
-void gemm_nn(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb,
+CME_MULTIVERSION void gemm_nn(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb,
              double* C, int64_t ldc) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < M; ++i) {
@@ -81,44 +97,56 @@ void gemm_nn(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, cons
     }
 }
 
-// C[M][N] = A[K][M]^T * B[K][N] + beta_c * Cadd[M][N] (Cadd may be null), row-major: 4 rows of C
-// at a time (a 4-wide column strip of A), j contiguous; k is walked in chunks so that the strip of
-// C being accumulated stays in cache.
-void gemm_tn(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb,
-             double* C, int64_t ldc, double beta_c, const double* Cadd, int64_t ldadd) {
+// C[M][N] = A[K][M]^T * B[K][N] + beta_c * Cadd[M][N] (Cadd may be null), row-major.  Threads take
+// column blocks of C: a block of B (K rows x ~N/threads columns) then stays in the core's L2 while
+// the rows of C are walked four at a time (a 4-wide column strip of A, j contiguous).  Splitting
+// over the rows of C instead made every thread stream all of B once per strip: 125 MB of traffic
+// per step of the 784-100-10 model, which was most of its time.
+CME_MULTIVERSION void gemm_tn(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B,
+                              int64_t ldb, double* C, int64_t ldc, double beta_c, const double* Cadd,
+                              int64_t ldadd) {
+    int nthreads = 1;
+#ifdef _OPENMP
+    nthreads = omp_get_max_threads();
+#endif
+    int64_t NB = ((N + nthreads - 1) / nthreads + 7) / 8 * 8;
+    if (NB < 8) NB = 8;
 #pragma omp parallel for schedule(static)
-    for (int64_t i0 = 0; i0 < M; i0 += 4) {
-        const int64_t mi = std::min<int64_t>(4, M - i0);
-        for (int64_t i = 0; i < mi; ++i) {
-            double* c = C + (i0 + i) * ldc;
-            if (Cadd) {
-                const double* w = Cadd + (i0 + i) * ldadd;
-                for (int64_t j = 0; j < N; ++j) c[j] = beta_c * w[j];
-            } else {
-                for (int64_t j = 0; j < N; ++j) c[j] = 0.0;
-            }
-        }
-        for (int64_t k = 0; k < K; ++k) {
-            const double* b = B + k * ldb;
-            const double* a = A + k * lda + i0;
-            if (mi == 4) {
-                const double x0 = a[0], x1 = a[1], x2 = a[2], x3 = a[3];
-                double *c0 = C + (i0 + 0) * ldc, *c1 = C + (i0 + 1) * ldc, *c2 = C + (i0 + 2) * ldc,
-                       *c3 = C + (i0 + 3) * ldc;
-#pragma omp simd
-                for (int64_t j = 0; j < N; ++j) {
-                    const double y = b[j];
-                    c0[j] += x0 * y;
-                    c1[j] += x1 * y;
-                    c2[j] += x2 * y;
-                    c3[j] += x3 * y;
+    for (int64_t jb = 0; jb < N; jb += NB) {
+        const int64_t je = std::min<int64_t>(N, jb + NB);
+        for (int64_t i0 = 0; i0 < M; i0 += 4) {
+            const int64_t mi = std::min<int64_t>(4, M - i0);
+            for (int64_t i = 0; i < mi; ++i) {
+                double* c = C + (i0 + i) * ldc;
+                if (Cadd) {
+                    const double* w = Cadd + (i0 + i) * ldadd;
+                    for (int64_t j = jb; j < je; ++j) c[j] = beta_c * w[j];
+                } else {
+                    for (int64_t j = jb; j < je; ++j) c[j] = 0.0;
                 }
-            } else {
-                for (int64_t i = 0; i < mi; ++i) {
-                    const double x = a[i];
-                    double* c = C + (i0 + i) * ldc;
+            }
+            for (int64_t k = 0; k < K; ++k) {
+                const double* b = B + k * ldb;
+                const double* a = A + k * lda + i0;
+                if (mi == 4) {
+                    const double x0 = a[0], x1 = a[1], x2 = a[2], x3 = a[3];
+                    double *c0 = C + (i0 + 0) * ldc, *c1 = C + (i0 + 1) * ldc, *c2 = C + (i0 + 2) * ldc,
+                           *c3 = C + (i0 + 3) * ldc;
 #pragma omp simd
-                    for (int64_t j = 0; j < N; ++j) c[j] += x * b[j];
+                    for (int64_t j = jb; j < je; ++j) {
+                        const double y = b[j];
+                        c0[j] += x0 * y;
+                        c1[j] += x1 * y;
+                        c2[j] += x2 * y;
+                        c3[j] += x3 * y;
+                    }
+                } else {
+                    for (int64_t i = 0; i < mi; ++i) {
+                        const double x = a[i];
+                        double* c = C + (i0 + i) * ldc;
+#pragma omp simd
+                        for (int64_t j = jb; j < je; ++j) c[j] += x * b[j];
+                    }
                 }
             }
         }
