@@ -128,7 +128,13 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
     if ex_src.exists() and (force or _newer(ex_bin, [ex_src, dev_lib] + headers)):
         _run([nvcc, "-O2", "-std=c++17", "-I", str(INC), str(ex_src), "-o", str(ex_bin),
               "-L", str(LIBDIR), "-lcme213b", "-Xlinker", "-rpath=$ORIGIN"], None, verbose)
-    return {"device": dev_lib, "host": host_lib, "example": ex_bin}
+    # --- the same for the host library alone: the serial CPU trainer from C++ (plain g++) ---
+    cpu_src = ROOT / "examples" / "train_mlp_cpu.cpp"
+    cpu_bin = LIBDIR / "train_mlp_cpu_example"
+    if cpu_src.exists() and (force or _newer(cpu_bin, [cpu_src, host_lib] + headers)):
+        _run([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-I", str(INC), str(cpu_src), "-o", str(cpu_bin),
+              "-L", str(LIBDIR), "-lcme213b_host", "-Wl,-rpath,$ORIGIN"], None, verbose)
+    return {"device": dev_lib, "host": host_lib, "example": ex_bin, "example_cpu": cpu_bin}
 
 
 def main(argv=None) -> int:

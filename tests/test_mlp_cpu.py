@@ -213,3 +213,13 @@ def test_native_cpp_serial_trainer_matches_the_torch_oracle():
     with pytest.raises(ValueError):
         host.mlp_train(x.double().numpy(), (lab + 20).numpy(), b.W[0].numpy().copy(), b.b[0].numpy().copy(),
                        b.W[1].numpy().copy(), b.b[1].numpy().copy(), 0.1, 0.0, 1, 800)
+
+
+def test_cpp_cpu_example_trains_on_the_host_library_alone():
+    """examples/train_mlp_cpu.cpp: the serial trainer from a C++ program that links only
+    libcme213b_host.so (no GPU, no Python)."""
+    from cme213_sp18_b200 import build
+
+    exe = build.build()["example_cpu"]
+    res = subprocess.run([str(exe), "48", "4000", "20", "1.0"], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and "TRAIN_CPU_OK" in res.stdout, res.stdout + res.stderr
